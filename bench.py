@@ -1,0 +1,425 @@
+#!/usr/bin/env python
+"""bench.py -- guesses scored per second on the BASELINE.json workload.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (BASELINE.json `metric`, configs[2]): batches of 4096 guesses x 16 word slots
+against a resident 3,000,000 x 300 fp32 table (the shape of word2vec-google-news-300,
+download_model.py:9), 2 hidden words per round (src/backend.py:49), ~5 % unknown words and
+~1 % exact matches.  Data are synthetic (cassmantle_b200/synth.py): no weights exist offline.
+
+A step = one pass of the hot path over one batch = one launch of cm_score_kernel.
+  value  : device-resident inputs, K steps timed with CUDA events on the launch stream,
+           max over ranks.  A ring of distinct batches is cycled so consecutive steps touch
+           different table rows (uniform over 3.6 GB >> 126 MB of L2).
+  e2e    : the same K steps through the C-ABI host entry point (cm_score_batch_host):
+           pinned host inputs -> H2D -> kernel -> D2H scores, synchronous per call.
+  roofline : the scoring kernel alone, >= 1 s of back-to-back launches timed with CUDA events;
+           achieved = algorithmic bytes (N*1204 + 8 per guess) / time.
+  cpu_baseline : the oracle's faithful per-pair port of src/backend.py:303-317 (what the
+           reference does) on this box's cores, bounded sample; rank 0, N = 1 only.
+
+`--impl reference` times that same CPU port alone, on the same config (the reference
+itself cannot run here: gensim is not installed and its weights cannot be downloaded).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+from cassmantle_b200 import synth  # noqa: E402
+
+V, D = synth.FULL_ROWS, synth.DIM
+B, N = 4096, 16
+N_ANSWERS = 2
+MIN_SCORE = 0.01
+RING = 64                      # distinct batches cycled through (64 x 79 MB of rows)
+BYTES_PER_GUESS = N * (D * 4 + 4) + 8      # N rows + N indices + len/slot + score
+METRIC = "guesses_scored_per_sec"
+UNIT = "guesses/s"
+WORKLOAD = (f"{B} guesses x {N} word slots per step, resident table {V}x{D} fp32 (3.6 GB), "
+            f"{N_ANSWERS} answers, 5% OOV, 1% exact; BASELINE.json configs[2]")
+
+
+def make_ring(seed0: int):
+    ring = []
+    ans = None
+    for i in range(RING):
+        idx, ln, a, slot, ex = synth.make_guess_batch(B, N, V, N_ANSWERS, seed=seed0 + i,
+                                                      near_frac=0.3 if i == 0 else 0.0)
+        if ans is None:
+            ans = a                      # one round: the answers stay, the guesses change
+        ring.append((idx, ln, slot, ex))
+    return ans, ring
+
+
+# ------------------------------------------------------------------------------------------
+# CPU legs (oracle port).  Workers are forked BEFORE any CUDA initialisation.
+# ------------------------------------------------------------------------------------------
+_CPU = {}
+
+
+def _cpu_worker(task):
+    from oracle import scorer_oracle as O
+    bi, lo, hi = task
+    idx, ln, slot, ex = _CPU["ring"][bi]
+    return O.score_batch_faithful(_CPU["table"], idx[lo:hi], ln[lo:hi], _CPU["ans"], slot[lo:hi],
+                                  ex[lo:hi], MIN_SCORE)
+
+
+class CpuScorer:
+    """Faithful per-pair port, spread over `workers` forked processes (one uvicorn worker each)."""
+
+    def __init__(self, ans, ring, workers: int):
+        import multiprocessing as mp
+        from oracle import c_oracle
+        self.workers = max(1, workers)
+        t0 = time.time()
+        _CPU["table"] = c_oracle.synth_fill(V, D, 0, threads=self.workers)
+        _CPU["ans"], _CPU["ring"] = ans, ring
+        self.table_seconds = time.time() - t0
+        self.pool = mp.get_context("fork").Pool(self.workers) if self.workers > 1 else None
+
+    def score(self, bi: int, n_guesses: int) -> np.ndarray:
+        """Score the first n_guesses of ring batch bi."""
+        if self.pool is None:
+            return _cpu_worker((bi, 0, n_guesses))
+        per = -(-n_guesses // self.workers)
+        tasks = [(bi, lo, min(lo + per, n_guesses)) for lo in range(0, n_guesses, per)]
+        return np.concatenate(self.pool.map(_cpu_worker, tasks, chunksize=1))
+
+    def close(self):
+        if self.pool is not None:
+            self.pool.close()
+            self.pool.join()
+        _CPU.clear()
+
+
+def calibrate(cpu: CpuScorer) -> float:
+    n = min(B, 64 * cpu.workers)
+    cpu.score(0, n)
+    t0 = time.perf_counter()
+    cpu.score(1, n)
+    return n / (time.perf_counter() - t0)
+
+
+def run_reference(args) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    workers = args.cpu_workers or os.cpu_count() or 1
+    ans, ring = make_ring(1000)
+    cpu = CpuScorer(ans, ring, workers)
+    rate = calibrate(cpu)
+    total_steps = args.steps + args.warmup
+    sample = int(max(16, min(B, rate * args.ref_budget_s / max(1, total_steps))))
+    for i in range(args.warmup):
+        cpu.score(i % RING, sample)
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        cpu.score((args.warmup + i) % RING, sample)
+    dt = time.perf_counter() - t0
+    cpu.close()
+    value = args.steps * sample / dt
+    desc = (f"first {sample} guesses of each {B}x{N} batch per step, {args.steps} steps, "
+            f"per-pair Python loop (oracle port of src/backend.py:303-317 + gensim similarity)")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample_guesses_per_step": sample,
+                   "note": "reference's CPU scorer restated (gensim absent offline); host cores only"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": workers, "kind": "port",
+                         "sample": desc},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    BAD = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20}
+    NOTE = {"sw_power_cap": 0x4}
+
+    def __init__(self, index: int, period: float = 0.02):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons = [], set()
+        self.sm_max = None
+        self._stop = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception as exc:      # pragma: no cover
+            self.err = repr(exc)
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+                for name, bit in {**self.BAD, **self.NOTE}.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(self.period)
+
+    def stop(self):
+        self._stop.set()
+        if self.is_alive():
+            self.join()
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------
+# own arm
+# ------------------------------------------------------------------------------------------
+def run_own(args) -> None:
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    ans, ring = make_ring(1000 + 7919 * rank)
+
+    # ---- CPU baseline first (rank 0, single-GPU run only), before CUDA is touched -------
+    cpu_baseline, cpu_check = None, None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        workers = args.cpu_workers or os.cpu_count() or 1
+        cpu = CpuScorer(ans, ring, workers)
+        rate = calibrate(cpu)
+        n_batches = int(max(1, min(RING, round(rate * args.cpu_budget_s / B))))
+        t0 = time.perf_counter()
+        outs = [cpu.score(i, B) for i in range(n_batches)]
+        dt = time.perf_counter() - t0
+        single = None
+        if workers > 1:                      # also the literal single-process figure
+            t1 = time.perf_counter()
+            _cpu_worker((0, 0, 512))
+            single = 512 / (time.perf_counter() - t1)
+        cpu.close()
+        cpu_check = outs
+        cpu_baseline = {
+            "value": n_batches * B / dt, "unit": UNIT, "cores": workers, "kind": "port",
+            "sample": f"{n_batches} batches of {B}x{N} ({n_batches * B} guesses, {dt:.1f} s), per-pair "
+                      f"Python loop = oracle port of src/backend.py:303-317 + gensim similarity, "
+                      f"one forked worker per core",
+            "single_process_value": single,
+        }
+
+    import torch
+    import torch.distributed as dist
+
+    from cassmantle_b200 import _lib
+    from cassmantle_b200.engine import ScoringEngine
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    lib = _lib.load()
+    eng = ScoringEngine.synthetic(V, D, seed=0, device=local_rank)
+    eng.set_answers(ans)
+    eng.synchronize()
+
+    # device-resident ring + pinned host ring
+    d_ring, h_ring = [], []
+    for idx, ln, slot, ex in ring:
+        d_ring.append(tuple(torch.from_numpy(a).to(dev) for a in (idx, ln, slot, ex)))
+        h_ring.append(tuple(torch.from_numpy(a).pin_memory() for a in (idx, ln, slot, ex)))
+    d_scores = torch.empty(B, dtype=torch.float32, device=dev)
+    gathered = torch.empty(world * B, dtype=torch.float32, device=dev) if world > 1 else None
+    h_scores = torch.empty(B, dtype=torch.float32).pin_memory()
+    stream = torch.cuda.current_stream()
+    st = stream.cuda_stream
+
+    def step_device(i: int) -> None:
+        t = d_ring[i % RING]
+        eng.score_device(t[0].data_ptr(), t[1].data_ptr(), B, N, t[2].data_ptr(), t[3].data_ptr(),
+                         MIN_SCORE, d_scores.data_ptr(), 0, stream=st)
+        if world > 1:        # north_star: per-guess scores are all-gathered over NVLink
+            dist.all_gather_into_tensor(gathered, d_scores)
+
+    h_np = [tuple(t.numpy() for t in tup) for tup in h_ring]
+    h_scores_np = h_scores.numpy()
+    score_host = lib.cm_score_batch_host
+    import ctypes
+    ms32 = ctypes.c_float(np.float32(MIN_SCORE))
+
+    def step_host(i: int) -> None:
+        a = h_np[i % RING]
+        rc = score_host(eng._h, a[0].ctypes.data, a[1].ctypes.data, B, N, a[2].ctypes.data,
+                        a[3].ctypes.data, ms32, h_scores_np.ctypes.data, None)
+        if rc != 0:
+            _lib.check(rc)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+
+    # ---- value: device-resident, K steps ------------------------------------------------
+    for i in range(args.warmup):
+        step_device(i)
+    barrier()
+    launches0 = lib.cm_kernel_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for i in range(args.steps):
+        step_device(args.warmup + i)
+    e1.record(stream)
+    barrier()
+    gpu_launches = int(lib.cm_kernel_launch_count() - launches0)
+    dev_ms = max_over_ranks(e0.elapsed_time(e1))
+    value = args.steps * B * world / (dev_ms * 1e-3)
+
+    # ---- roofline: the scoring kernel alone, >= ~1 s of launches -------------------------
+    per_step_ms = max(dev_ms / args.steps, 1e-3)
+    n_roof = int(min(200_000, max(2000, args.roofline_s * 1e3 / per_step_ms)))
+    t_ring = [(t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(), t[3].data_ptr()) for t in d_ring]
+    fn, h, out_p = lib.cm_score_batch_device, eng._h, d_scores.data_ptr()
+    for i in range(50):
+        p = t_ring[i % RING]
+        fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, st)
+    torch.cuda.synchronize()
+    r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    r0.record(stream)
+    for i in range(n_roof):
+        p = t_ring[i % RING]
+        fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, st)
+    r1.record(stream)
+    torch.cuda.synchronize()
+    kern_us = r0.elapsed_time(r1) * 1e3 / n_roof
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        with open(peaks_path) as f:
+            peak, peak_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    achieved = B * BYTES_PER_GUESS / (kern_us * 1e-6) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": TRAFFIC_BYTES_PER_LAUNCH,
+                "kernel": "cm_score_kernel<3>", "kernel_us": kern_us, "launches_timed": n_roof,
+                "algorithmic_bytes_per_launch": B * BYTES_PER_GUESS, "peak_source": peak_src}
+
+    # ---- e2e: host buffers through the C ABI ---------------------------------------------
+    for i in range(args.warmup):
+        step_host(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step_host(args.warmup + i)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    h2d = B * N * 4 + B * 4 + B * 4 + B
+    e2e = {"value": args.steps * B * world / e2e_s, "unit": UNIT,
+           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 4,
+           "ms_per_step": e2e_s / args.steps * 1e3,
+           "api": "cm_score_batch_host (C ABI, pinned host buffers, synchronous per call)"}
+
+    # ---- single-call latency on the micro-batch shape (configs[1]: 512 guesses x 8) ------
+    lat = None
+    if rank == 0:
+        idx8, ln8, _, slot8, ex8 = synth.make_guess_batch(512, 8, V, N_ANSWERS, seed=4242)
+        slot8 = np.ascontiguousarray(slot8)
+        out8 = np.empty(512, dtype=np.float32)
+        ts = []
+        for i in range(300):
+            t1 = time.perf_counter()
+            score_host(eng._h, idx8.ctypes.data, ln8.ctypes.data, 512, 8, slot8.ctypes.data,
+                       ex8.ctypes.data, ms32, out8.ctypes.data, None)
+            ts.append(time.perf_counter() - t1)
+        ts = np.sort(np.asarray(ts[50:])) * 1e6
+        lat = {"workload": "512 guesses x 8 slots, one host call (configs[1])",
+               "p50_us": float(ts[len(ts) // 2]), "p99_us": float(ts[int(len(ts) * 0.99)])}
+
+    clocks = sampler.stop()
+
+    # ---- parity spot check of the timed path against the CPU sample ----------------------
+    parity = None
+    if cpu_check is not None:
+        worst = 0.0
+        for i, want in enumerate(cpu_check[:4]):
+            step_host(i)
+            worst = max(worst, float(np.abs(h_scores_np - want).max()))
+        parity = {"batches": min(4, len(cpu_check)), "max_abs_diff_vs_oracle": worst}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "guesses_per_step_per_gpu": B, "word_slots": N,
+                       "parallelism": f"replica-per-gpu x{world}, batch sharded, "
+                                      + ("NCCL all_gather of scores" if world > 1 else "no collective"),
+                       "l2": f"ring of {RING} distinct batches over a 3.6 GB table (inputs >> L2)"},
+            "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
+            "cpu_baseline": cpu_baseline, "clocks": clocks, "latency": lat, "parity": parity,
+        }
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of cm_score_kernel at 4096x16 from the
+# committed `ncu --set full` capture (profiles/); None until a capture exists.
+TRAFFIC_BYTES_PER_LAUNCH = None
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--cpu-workers", type=int, default=0, help="0 = all cores")
+    ap.add_argument("--cpu-budget-s", type=float, default=12.0)
+    ap.add_argument("--ref-budget-s", type=float, default=60.0)
+    ap.add_argument("--roofline-s", type=float, default=1.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_own(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,111 @@
+"""Backend -- the scorer half of the reference's ``Backend`` class, on the GPU.
+
+Mirrors src/backend.py:303-317 name for name:
+
+    def compute_score(self, inputs: str, answer: str) -> float
+    async def compute_scores(self, data: Dict[str, Dict[str, str]]) -> Dict[str, str]
+
+so ``Server.compute_client_scores`` (src/server.py:63-76) and the browser
+(static/script.js:362-411) run unchanged.  Return values keep the reference's types and
+text: the Python float ``1.0`` for equal strings, the Python float ``min_score`` when the
+word is unknown or the cosine does not beat the floor, otherwise a ``numpy.float32``
+cosine; ``compute_scores`` returns ``str()`` of those.  Nothing here raises for an unknown
+word (the reference swallows the KeyError, src/backend.py:308-309).
+
+What changed underneath: ``self.wv.similarity`` is one batched CUDA launch over a table
+replica resident in HBM (include/cassmantle_b200.h).  There is no CPU path.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from ._lib import CM_MAX_ANSWERS
+from .engine import ScoringEngine
+from .vocab import Vocabulary
+
+
+class Backend:
+    def __init__(self, engine: ScoringEngine, vocab: Vocabulary, min_score: float = 0.1,
+                 phrase_guesses: bool = False, max_words: int = 64) -> None:
+        # min_score default as src/backend.py:22; Server overrides it to 0.01 (src/server.py:17)
+        self.min_score = min_score
+        self.engine = engine
+        self.vocab = vocab
+        self.num_masked = 2                       # src/backend.py:49
+        # Extension switch (SURVEY.md §0 Track A): treat a guess as a phrase, mean-pooled
+        # like gensim's n_similarity.  Off by default: the reference looks the whole string
+        # up as one key, so "two words" is simply unknown there.
+        self.phrase_guesses = phrase_guesses
+        self.max_words = max_words
+        self._answer_rows: List[int] = []
+        self._answer_slot: Dict[int, int] = {}
+
+    # ---- answers: registered with the engine, reused while the round lasts -----------
+    def _slots_for(self, rows: Sequence[int]) -> List[int]:
+        new = [r for r in dict.fromkeys(rows) if r not in self._answer_slot]
+        if new:
+            if len(self._answer_rows) + len(new) > CM_MAX_ANSWERS:
+                self._answer_rows, self._answer_slot = [], {}
+                new = list(dict.fromkeys(rows))
+                if len(new) > CM_MAX_ANSWERS:
+                    raise ValueError(f"more than {CM_MAX_ANSWERS} distinct answers in one batch")
+            for r in new:
+                self._answer_slot[r] = len(self._answer_rows)
+                self._answer_rows.append(r)
+            self.engine.set_answers(self._answer_rows)
+        return [self._answer_slot[r] for r in rows]
+
+    # ---- core: a list of (guess, answer) string pairs -> reference-typed scores ------
+    def score_pairs(self, pairs: Sequence[Tuple[str, str]]) -> list:
+        if not pairs:
+            return []
+        B = len(pairs)
+        lookup = self.vocab.lookup
+        words: List[List[str]] = []
+        exact = np.zeros(B, dtype=np.uint8)
+        ans_rows: List[int] = []
+        for b, (inputs, answer) in enumerate(pairs):
+            inputs, answer = inputs.lower(), answer.lower()          # backend.py:304
+            exact[b] = inputs == answer                              # backend.py:305
+            if self.phrase_guesses:
+                w = inputs.split()[: self.max_words]
+            else:
+                w = [inputs]
+            words.append(w)
+            ans_rows.append(lookup(answer))
+        N = max(1, max(len(w) for w in words))
+        idx = np.full((B, N), -1, dtype=np.int32)
+        length = np.zeros(B, dtype=np.int32)
+        for b, w in enumerate(words):
+            length[b] = len(w)
+            for k, t in enumerate(w):
+                idx[b, k] = lookup(t)
+        slots = np.asarray(self._slots_for(ans_rows), dtype=np.int32)
+        scores, _ = self.engine.score_host(idx, length, slots, exact, self.min_score)
+        floor32 = np.float32(self.min_score)
+        out = []
+        for b in range(B):
+            if exact[b]:
+                out.append(1.0)
+            elif scores[b] > floor32:
+                out.append(scores[b])            # numpy.float32, like wv.similarity's result
+            else:
+                out.append(self.min_score)       # the Python float, like max(min_score, .)
+        return out
+
+    # ---- the reference's two methods ---------------------------------------------------
+    def compute_score(self, inputs: str, answer: str) -> float:
+        return self.score_pairs([(inputs, answer)])[0]
+
+    async def compute_scores(self, data: Dict[str, Dict[str, str]]) -> Dict[str, str]:
+        keys = list(data.keys())
+        vals = self.score_pairs([(data[k]["input"], data[k]["answer"]) for k in keys])
+        scores: Dict[str, str] = {}
+        for key, score in zip(keys, vals):
+            scores.update({key: str(score)})                          # backend.py:316
+        return scores
+
+    def score_to_blur(self, score: float, min_blur: float = 0.0, max_blur: float = 15):
+        return min_blur + (1 - score ** 2) * (max_blur - min_blur)    # backend.py:319-320

@@ -1,0 +1,558 @@
+// cassmantle_b200 -- guess-scoring kernels and their C ABI (include/cassmantle_b200.h).
+//
+// Hot path replaced: Backend.compute_score / compute_scores, src/backend.py:303-317, i.e.
+// gensim KeyedVectors.similarity (src/backend.py:307) = dot(unitvec(row_a), unitvec(row_b)).
+// Everything here is an HBM-bound gather: one 1200-byte table row per guessed word, summed
+// in fp32 in word order (numpy mean(axis=0)), normalised through an fp64 norm (gensim binds
+// the double-precision BLAS nrm2/scal), dotted in fp32 with the answer's unit vector,
+// floored at min_score.  There is no dense contraction on this path, so no tensor-core work.
+//
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a (see cassmantle_b200/build.py).
+
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+
+#include "../../include/cassmantle_b200.h"
+#include "cm_common.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<int64_t> g_launches{0};
+
+int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CM_CUDA(expr)                                                                   \
+    do {                                                                                \
+        cudaError_t err__ = (expr);                                                     \
+        if (err__ != cudaSuccess)                                                       \
+            return fail(CM_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(err__)); \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+    }
+    ~DeviceGuard() {
+        int cur = -1;
+        if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+    }
+};
+
+constexpr int kWarpsPerCta = 8;
+constexpr int kRowsInFlight = 4;   // table rows a warp requests before it starts adding
+
+// --------------------------------------------------------------------------------------
+// Synthetic table fill -- bit-identical to cassmantle_b200/synth.py: table_rows().
+// --------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+cm_synth_fill_kernel(float *__restrict__ table, int64_t n_rows, int dim, uint32_t seed) {
+    const uint32_t k_noise = cm::mix32(seed ^ 0x9e3779b9u);
+    const uint32_t k_clu = cm::mix32(seed ^ 0x85ebca6bu);
+    const uint32_t k_cen = cm::mix32(seed ^ 0xc2b2ae35u);
+    const float inv_unit = (float)(1.0 / 3620.0);
+    const int dim4 = dim >> 2;
+    const int64_t total = n_rows * dim4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t row = (uint32_t)(i / dim4);
+        const uint32_t c0 = (uint32_t)(i % dim4) * 4u;
+        const uint32_t hs = cm::mix32(row * 0x9e3779b1u + seed);
+        const float u = __fmul_rn(__uint2float_rn(hs >> 8), 5.9604644775390625e-08f);  // 2^-24
+        const float coef = __fmul_rn(__fadd_rn(0.5f, __fmul_rn(4.5f, u)), inv_unit);
+        const uint32_t clu = cm::mix32(row ^ k_clu) & 1023u;
+        float v[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const uint32_t col = c0 + t;
+            const int s = cm::bytesum(cm::mix32((row * (uint32_t)dim + col) ^ k_noise)) +
+                          cm::bytesum(cm::mix32((clu * (uint32_t)dim + col) ^ k_cen));
+            v[t] = __fmul_rn(__int2float_rn(s), coef);
+        }
+        reinterpret_cast<float4 *>(table)[i] = make_float4(v[0], v[1], v[2], v[3]);
+    }
+}
+
+// --------------------------------------------------------------------------------------
+// unitvec() in registers.  Lane `l` of a warp holds float4 vectors l, l+32, ... of one row.
+// gensim matutils.unitvec: veclen = dnrm2(v); v * (1/veclen) in fp64, cast back to fp32;
+// a zero vector is returned unchanged.
+// --------------------------------------------------------------------------------------
+template <int VPL>
+__device__ __forceinline__ void warp_unitvec(float4 (&m)[VPL]) {
+    double ss = 0.0;
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+        ss = fma((double)m[v].x, (double)m[v].x, ss);
+        ss = fma((double)m[v].y, (double)m[v].y, ss);
+        ss = fma((double)m[v].z, (double)m[v].z, ss);
+        ss = fma((double)m[v].w, (double)m[v].w, ss);
+    }
+    ss = cm::warp_sum(ss);
+    if (ss > 0.0) {
+        const double inv = 1.0 / sqrt(ss);
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+            m[v].x = (float)((double)m[v].x * inv);
+            m[v].y = (float)((double)m[v].y * inv);
+            m[v].z = (float)((double)m[v].z * inv);
+            m[v].w = (float)((double)m[v].w * inv);
+        }
+    }
+}
+
+// One warp per registered answer: ans_unit[a] = unitvec(table[answer_rows[a]]).
+template <int VPL>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+cm_answer_unit_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
+                      const int32_t *__restrict__ answer_rows, int n_answers,
+                      float *__restrict__ ans_unit) {
+    const int lane = threadIdx.x & 31;
+    const int a = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
+    if (a >= n_answers) return;
+    const int32_t r = answer_rows[a];
+    const bool in_vocab = r >= 0 && (int64_t)r < n_rows;
+    float4 m[VPL];
+    const float4 *src = reinterpret_cast<const float4 *>(table) + (size_t)(in_vocab ? r : 0) * dim4;
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+        const int j = lane + 32 * v;
+        m[v] = (in_vocab && j < dim4) ? __ldg(src + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    warp_unitvec<VPL>(m);
+    float4 *dst = reinterpret_cast<float4 *>(ans_unit) + (size_t)a * dim4;
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+        const int j = lane + 32 * v;
+        if (j < dim4) dst[j] = m[v];
+    }
+}
+
+// --------------------------------------------------------------------------------------
+// The scoring kernel: one warp per guess.
+//   gather N rows (streaming 16-byte loads, kRowsInFlight rows requested at a time)
+//   -> fp32 in-order sum -> / N -> unitvec (fp64 norm) -> fp32 dot with the answer's unit
+//   vector -> floor at min_score -> fp32 score (+ optional hundredths of a percent).
+// --------------------------------------------------------------------------------------
+template <int VPL>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
+                const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
+                int n_guesses, int n_slots,
+                const float *__restrict__ ans_unit, const int32_t *__restrict__ ans_rows,
+                int n_answers, const int32_t *__restrict__ answer_slot,
+                const uint8_t *__restrict__ exact, float min_score,
+                float *__restrict__ scores, int32_t *__restrict__ centi) {
+    const int lane = threadIdx.x & 31;
+    const int b = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
+    if (b >= n_guesses) return;
+
+    float result;
+    if (exact != nullptr && exact[b] != 0) {
+        result = 1.0f;                                     // src/backend.py:305
+    } else {
+        int n = guess_len[b];
+        n = n < 0 ? 0 : (n > n_slots ? n_slots : n);
+        const int slot = answer_slot[b];
+        const int32_t *gi = guess_idx + (size_t)b * n_slots;
+
+        // KeyError scan: any used slot outside the table, an empty guess, or an unknown answer.
+        bool bad = false;
+        for (int c = lane; c < n; c += 32) {
+            const int32_t r = gi[c];
+            bad |= (r < 0) || ((int64_t)r >= n_rows);
+        }
+        bad = __any_sync(cm::kFullMask, bad) || n == 0 || slot < 0 || slot >= n_answers;
+        if (!bad) {
+            const int32_t ar = ans_rows[slot];
+            bad = ar < 0 || (int64_t)ar >= n_rows;
+        }
+
+        if (bad) {
+            result = min_score;                            // src/backend.py:308-310
+        } else {
+            float4 acc[VPL];
+#pragma unroll
+            for (int v = 0; v < VPL; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+            for (int c = 0; c < n; c += 32) {
+                const int m = min(32, n - c);
+                const int32_t mine = (lane < m) ? gi[c + lane] : 0;
+                for (int k = 0; k < m; k += kRowsInFlight) {
+                    float4 buf[kRowsInFlight][VPL];
+#pragma unroll
+                    for (int i = 0; i < kRowsInFlight; ++i) {
+                        const int32_t r = __shfl_sync(cm::kFullMask, mine, (k + i) & 31);
+                        const bool live = (k + i) < m;
+                        const float4 *src = reinterpret_cast<const float4 *>(table) + (size_t)r * dim4;
+#pragma unroll
+                        for (int v = 0; v < VPL; ++v) {
+                            const int j = lane + 32 * v;
+                            buf[i][v] = (live && j < dim4) ? cm::ld_stream_f4(src + j)
+                                                           : make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < kRowsInFlight; ++i) {
+#pragma unroll
+                        for (int v = 0; v < VPL; ++v) {          // word order, like mean(axis=0)
+                            acc[v].x += buf[i][v].x;
+                            acc[v].y += buf[i][v].y;
+                            acc[v].z += buf[i][v].z;
+                            acc[v].w += buf[i][v].w;
+                        }
+                    }
+                }
+            }
+            if (n > 1) {
+                const float fn = (float)n;
+#pragma unroll
+                for (int v = 0; v < VPL; ++v) {
+                    acc[v].x = __fdiv_rn(acc[v].x, fn);
+                    acc[v].y = __fdiv_rn(acc[v].y, fn);
+                    acc[v].z = __fdiv_rn(acc[v].z, fn);
+                    acc[v].w = __fdiv_rn(acc[v].w, fn);
+                }
+            }
+            warp_unitvec<VPL>(acc);
+
+            const float4 *u = reinterpret_cast<const float4 *>(ans_unit) + (size_t)slot * dim4;
+            float p = 0.f;
+#pragma unroll
+            for (int v = 0; v < VPL; ++v) {
+                const int j = lane + 32 * v;
+                if (j < dim4) {
+                    const float4 w = __ldg(u + j);
+                    p = fmaf(acc[v].x, w.x, p);
+                    p = fmaf(acc[v].y, w.y, p);
+                    p = fmaf(acc[v].z, w.z, p);
+                    p = fmaf(acc[v].w, w.w, p);
+                }
+            }
+            p = cm::warp_sum(p);
+            result = (p > min_score) ? p : min_score;      // max(min_score, score): NaN -> min
+        }
+    }
+    if (lane == 0) {
+        scores[b] = result;
+        if (centi != nullptr) centi[b] = (int32_t)floor((double)result * 10000.0 + 0.5);
+    }
+}
+
+}  // namespace
+
+struct cm_engine {
+    int device = 0;
+    int64_t n_rows = 0;
+    int dim = 0;
+    float *d_table = nullptr;
+    float *d_ans_unit = nullptr;     // [CM_MAX_ANSWERS][dim] unit vectors of the round's answers
+    int32_t *d_ans_rows = nullptr;   // [CM_MAX_ANSWERS] their table rows (-1 = not in vocabulary)
+    int n_answers = 0;
+    cudaStream_t stream = nullptr;
+    // staging for the host-buffer entry point (grown on demand, reused across calls)
+    unsigned char *d_stage = nullptr;
+    unsigned char *h_stage = nullptr;
+    size_t stage_bytes = 0;
+    std::mutex mu;
+};
+
+namespace {
+
+template <int VPL>
+void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
+                  const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
+                  int32_t *centi, cudaStream_t st) {
+    const int grid = (B + kWarpsPerCta - 1) / kWarpsPerCta;
+    cm_score_kernel<VPL><<<grid, kWarpsPerCta * 32, 0, st>>>(
+        e->d_table, e->n_rows, e->dim / 4, gi, gl, B, N, e->d_ans_unit, e->d_ans_rows,
+        e->n_answers, slot, exact, min_score, scores, centi);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+}
+
+template <int VPL>
+void launch_answers(const cm_engine *e, const int32_t *d_rows, int A, cudaStream_t st) {
+    const int grid = (A + kWarpsPerCta - 1) / kWarpsPerCta;
+    cm_answer_unit_kernel<VPL><<<grid, kWarpsPerCta * 32, 0, st>>>(
+        e->d_table, e->n_rows, e->dim / 4, d_rows, A, e->d_ans_unit);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+}
+
+#define CM_DISPATCH_VPL(dim, CALL)                          \
+    switch (((dim) / 4 + 31) / 32) {                        \
+        case 1: CALL(1); break;                             \
+        case 2: CALL(2); break;                             \
+        case 3: CALL(3); break;                             \
+        case 4: CALL(4); break;                             \
+        case 5: CALL(5); break;                             \
+        case 6: CALL(6); break;                             \
+        case 7: CALL(7); break;                             \
+        default: CALL(8); break;                            \
+    }
+
+int check_engine(const cm_engine *e) {
+    if (e == nullptr) return fail(CM_ERR_INVALID, "engine is NULL");
+    if (e->d_table == nullptr) return fail(CM_ERR_STATE, "engine has no resident table");
+    return CM_OK;
+}
+
+int ensure_stage(cm_engine *e, size_t bytes) {
+    if (bytes <= e->stage_bytes) return CM_OK;
+    size_t want = e->stage_bytes ? e->stage_bytes : (size_t)1 << 20;
+    while (want < bytes) want *= 2;
+    if (e->d_stage) cudaFree(e->d_stage);
+    if (e->h_stage) cudaFreeHost(e->h_stage);
+    e->d_stage = nullptr; e->h_stage = nullptr; e->stage_bytes = 0;
+    if (cudaMalloc(&e->d_stage, want) != cudaSuccess) {
+        cudaGetLastError();
+        return fail(CM_ERR_NOMEM, "cudaMalloc of %zu staging bytes failed", want);
+    }
+    if (cudaHostAlloc(&e->h_stage, want, cudaHostAllocDefault) != cudaSuccess) {
+        cudaGetLastError();
+        cudaFree(e->d_stage); e->d_stage = nullptr;
+        return fail(CM_ERR_NOMEM, "cudaHostAlloc of %zu staging bytes failed", want);
+    }
+    e->stage_bytes = want;
+    return CM_OK;
+}
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+}  // namespace
+
+// ======================================================================================
+// C ABI
+// ======================================================================================
+extern "C" {
+
+const char *cm_last_error(void) { return g_err; }
+const char *cm_version(void) { return "0.1.0"; }
+int64_t cm_kernel_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int cm_engine_create(cm_engine **out, int device, int64_t n_rows, int dim) {
+    if (out == nullptr) return fail(CM_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    if (n_rows <= 0 || n_rows > 0x7fffffffLL)
+        return fail(CM_ERR_INVALID, "n_rows %lld outside [1, 2^31)", (long long)n_rows);
+    if (dim < 4 || dim > CM_MAX_DIM || dim % 4 != 0)
+        return fail(CM_ERR_INVALID, "dim %d must be a multiple of 4 in [4, %d]", dim, CM_MAX_DIM);
+    int n_dev = 0;
+    CM_CUDA(cudaGetDeviceCount(&n_dev));
+    if (device < 0 || device >= n_dev)
+        return fail(CM_ERR_INVALID, "device %d not in [0, %d)", device, n_dev);
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(CM_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+    cudaDeviceProp prop;
+    CM_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10)
+        return fail(CM_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only",
+                    device, prop.major, prop.minor);
+    cm_engine *e = new (std::nothrow) cm_engine();
+    if (e == nullptr) return fail(CM_ERR_NOMEM, "engine allocation failed");
+    e->device = device; e->n_rows = n_rows; e->dim = dim;
+    const size_t table_bytes = (size_t)n_rows * dim * sizeof(float);
+    cudaError_t err = cudaMalloc(&e->d_table, table_bytes);
+    if (err == cudaSuccess) err = cudaMalloc(&e->d_ans_unit, (size_t)CM_MAX_ANSWERS * dim * sizeof(float));
+    if (err == cudaSuccess) err = cudaMalloc(&e->d_ans_rows, (size_t)CM_MAX_ANSWERS * sizeof(int32_t));
+    if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    if (err != cudaSuccess) {
+        cudaGetLastError();
+        const int code = fail(err == cudaErrorMemoryAllocation ? CM_ERR_NOMEM : CM_ERR_CUDA,
+                              "engine setup (%zu table bytes) failed: %s", table_bytes,
+                              cudaGetErrorString(err));
+        cm_engine_destroy(e);
+        return code;
+    }
+    *out = e;
+    return CM_OK;
+}
+
+int cm_engine_destroy(cm_engine *e) {
+    if (e == nullptr) return CM_OK;
+    {
+        DeviceGuard guard(e->device);
+        if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
+        if (e->d_table) cudaFree(e->d_table);
+        if (e->d_ans_unit) cudaFree(e->d_ans_unit);
+        if (e->d_ans_rows) cudaFree(e->d_ans_rows);
+        if (e->d_stage) cudaFree(e->d_stage);
+        if (e->h_stage) cudaFreeHost(e->h_stage);
+    }
+    delete e;
+    return CM_OK;
+}
+
+int cm_engine_upload_rows(cm_engine *e, const float *rows, int64_t row0, int64_t n) {
+    if (int rc = check_engine(e)) return rc;
+    if (rows == nullptr) return fail(CM_ERR_INVALID, "rows is NULL");
+    if (row0 < 0 || n < 0 || row0 + n > e->n_rows)
+        return fail(CM_ERR_INVALID, "rows [%lld, %lld) outside the %lld-row table",
+                    (long long)row0, (long long)(row0 + n), (long long)e->n_rows);
+    DeviceGuard guard(e->device);
+    CM_CUDA(cudaMemcpyAsync(e->d_table + (size_t)row0 * e->dim, rows,
+                            (size_t)n * e->dim * sizeof(float), cudaMemcpyHostToDevice, e->stream));
+    CM_CUDA(cudaStreamSynchronize(e->stream));
+    return CM_OK;
+}
+
+int cm_engine_download_rows(cm_engine *e, float *rows, int64_t row0, int64_t n) {
+    if (int rc = check_engine(e)) return rc;
+    if (rows == nullptr) return fail(CM_ERR_INVALID, "rows is NULL");
+    if (row0 < 0 || n < 0 || row0 + n > e->n_rows)
+        return fail(CM_ERR_INVALID, "rows [%lld, %lld) outside the %lld-row table",
+                    (long long)row0, (long long)(row0 + n), (long long)e->n_rows);
+    DeviceGuard guard(e->device);
+    CM_CUDA(cudaMemcpyAsync(rows, e->d_table + (size_t)row0 * e->dim,
+                            (size_t)n * e->dim * sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+    CM_CUDA(cudaStreamSynchronize(e->stream));
+    return CM_OK;
+}
+
+int cm_engine_fill_synthetic(cm_engine *e, uint32_t seed) {
+    if (int rc = check_engine(e)) return rc;
+    if ((uint64_t)e->n_rows * (uint64_t)e->dim > 0xffffffffull)
+        return fail(CM_ERR_INVALID, "synthetic fill needs n_rows*dim < 2^32");
+    DeviceGuard guard(e->device);
+    cm_synth_fill_kernel<<<148 * 8, 256, 0, e->stream>>>(e->d_table, e->n_rows, e->dim, seed);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    CM_CUDA(cudaGetLastError());
+    CM_CUDA(cudaStreamSynchronize(e->stream));
+    return CM_OK;
+}
+
+int cm_engine_table(cm_engine *e, void **d_table, int64_t *n_rows, int *dim) {
+    if (int rc = check_engine(e)) return rc;
+    if (d_table) *d_table = e->d_table;
+    if (n_rows) *n_rows = e->n_rows;
+    if (dim) *dim = e->dim;
+    return CM_OK;
+}
+
+int cm_engine_stream(cm_engine *e, void **stream) {
+    if (e == nullptr || stream == nullptr) return fail(CM_ERR_INVALID, "NULL argument");
+    *stream = e->stream;
+    return CM_OK;
+}
+
+int cm_engine_synchronize(cm_engine *e) {
+    if (e == nullptr) return fail(CM_ERR_INVALID, "engine is NULL");
+    DeviceGuard guard(e->device);
+    CM_CUDA(cudaStreamSynchronize(e->stream));
+    return CM_OK;
+}
+
+int cm_set_answers_device(cm_engine *e, const int32_t *d_answer_rows, int n_answers, void *stream) {
+    if (int rc = check_engine(e)) return rc;
+    if (d_answer_rows == nullptr) return fail(CM_ERR_INVALID, "answer_rows is NULL");
+    if (n_answers < 1 || n_answers > CM_MAX_ANSWERS)
+        return fail(CM_ERR_INVALID, "n_answers %d outside [1, %d]", n_answers, CM_MAX_ANSWERS);
+    DeviceGuard guard(e->device);
+    cudaStream_t st = stream ? (cudaStream_t)stream : e->stream;
+    if (d_answer_rows != e->d_ans_rows)
+        CM_CUDA(cudaMemcpyAsync(e->d_ans_rows, d_answer_rows, (size_t)n_answers * sizeof(int32_t),
+                                cudaMemcpyDeviceToDevice, st));
+    e->n_answers = n_answers;
+#define CM_CALL(V) launch_answers<V>(e, e->d_ans_rows, n_answers, st)
+    CM_DISPATCH_VPL(e->dim, CM_CALL)
+#undef CM_CALL
+    CM_CUDA(cudaGetLastError());
+    return CM_OK;
+}
+
+int cm_set_answers(cm_engine *e, const int32_t *answer_rows, int n_answers, void *stream) {
+    if (int rc = check_engine(e)) return rc;
+    if (answer_rows == nullptr) return fail(CM_ERR_INVALID, "answer_rows is NULL");
+    if (n_answers < 1 || n_answers > CM_MAX_ANSWERS)
+        return fail(CM_ERR_INVALID, "n_answers %d outside [1, %d]", n_answers, CM_MAX_ANSWERS);
+    DeviceGuard guard(e->device);
+    cudaStream_t st = stream ? (cudaStream_t)stream : e->stream;
+    // pageable source: the runtime stages it before returning, so the caller's buffer is free
+    CM_CUDA(cudaMemcpyAsync(e->d_ans_rows, answer_rows, (size_t)n_answers * sizeof(int32_t),
+                            cudaMemcpyHostToDevice, st));
+    return cm_set_answers_device(e, e->d_ans_rows, n_answers, st);
+}
+
+int cm_score_batch_device(cm_engine *e, const int32_t *d_guess_idx, const int32_t *d_guess_len,
+                          int n_guesses, int n_slots, const int32_t *d_answer_slot,
+                          const uint8_t *d_exact, float min_score, float *d_scores,
+                          int32_t *d_centi, void *stream) {
+    if (int rc = check_engine(e)) return rc;
+    if (n_guesses < 0) return fail(CM_ERR_INVALID, "n_guesses %d is negative", n_guesses);
+    if (n_slots < 1 || n_slots > CM_MAX_SEQ)
+        return fail(CM_ERR_INVALID, "n_slots %d outside [1, %d]", n_slots, CM_MAX_SEQ);
+    if (n_guesses == 0) return CM_OK;
+    if (!d_guess_idx || !d_guess_len || !d_answer_slot || !d_scores)
+        return fail(CM_ERR_INVALID, "a required device pointer is NULL");
+    if (e->n_answers < 1) return fail(CM_ERR_STATE, "cm_set_answers has not been called");
+    DeviceGuard guard(e->device);
+    cudaStream_t st = stream ? (cudaStream_t)stream : e->stream;
+#define CM_CALL(V) launch_score<V>(e, d_guess_idx, d_guess_len, n_guesses, n_slots, \
+                                   d_answer_slot, d_exact, min_score, d_scores, d_centi, st)
+    CM_DISPATCH_VPL(e->dim, CM_CALL)
+#undef CM_CALL
+    CM_CUDA(cudaGetLastError());
+    return CM_OK;
+}
+
+int cm_score_batch_host(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_len,
+                        int n_guesses, int n_slots, const int32_t *answer_slot,
+                        const uint8_t *exact, float min_score, float *scores, int32_t *centi) {
+    if (int rc = check_engine(e)) return rc;
+    if (n_guesses < 0) return fail(CM_ERR_INVALID, "n_guesses %d is negative", n_guesses);
+    if (n_slots < 1 || n_slots > CM_MAX_SEQ)
+        return fail(CM_ERR_INVALID, "n_slots %d outside [1, %d]", n_slots, CM_MAX_SEQ);
+    if (n_guesses == 0) return CM_OK;
+    if (!guess_idx || !guess_len || !answer_slot || !scores)
+        return fail(CM_ERR_INVALID, "a required host pointer is NULL");
+    if (e->n_answers < 1) return fail(CM_ERR_STATE, "cm_set_answers has not been called");
+
+    std::lock_guard<std::mutex> lock(e->mu);     // one staging area: callers take turns
+    DeviceGuard guard(e->device);
+    const size_t B = (size_t)n_guesses, N = (size_t)n_slots;
+    // one packed block each way: [idx | len | slot | exact] in, [scores | centi] out
+    const size_t off_idx = 0;
+    const size_t off_len = off_idx + B * N * 4;
+    const size_t off_slot = off_len + B * 4;
+    const size_t off_exact = off_slot + B * 4;
+    const size_t in_bytes = align_up(off_exact + (exact ? B : 0), 256);
+    const size_t off_scores = in_bytes;
+    const size_t off_centi = off_scores + B * 4;
+    const size_t total = align_up(off_centi + (centi ? B * 4 : 0), 256);
+    if (int rc = ensure_stage(e, total)) return rc;
+
+    memcpy(e->h_stage + off_idx, guess_idx, B * N * 4);
+    memcpy(e->h_stage + off_len, guess_len, B * 4);
+    memcpy(e->h_stage + off_slot, answer_slot, B * 4);
+    if (exact) memcpy(e->h_stage + off_exact, exact, B);
+    CM_CUDA(cudaMemcpyAsync(e->d_stage, e->h_stage, in_bytes, cudaMemcpyHostToDevice, e->stream));
+    int rc = cm_score_batch_device(
+        e, (const int32_t *)(e->d_stage + off_idx), (const int32_t *)(e->d_stage + off_len),
+        n_guesses, n_slots, (const int32_t *)(e->d_stage + off_slot),
+        exact ? (const uint8_t *)(e->d_stage + off_exact) : nullptr, min_score,
+        (float *)(e->d_stage + off_scores), centi ? (int32_t *)(e->d_stage + off_centi) : nullptr,
+        e->stream);
+    if (rc != CM_OK) return rc;
+    CM_CUDA(cudaMemcpyAsync(e->h_stage + off_scores, e->d_stage + off_scores, total - in_bytes,
+                            cudaMemcpyDeviceToHost, e->stream));
+    CM_CUDA(cudaStreamSynchronize(e->stream));
+    memcpy(scores, e->h_stage + off_scores, B * 4);
+    if (centi) memcpy(centi, e->h_stage + off_centi, B * 4);
+    return CM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,134 @@
+"""ScoringEngine -- Python owner of one cm_engine (one GPU, one resident table replica).
+
+Takes the place of the ``KeyedVectors`` object the reference keeps in ``self.wv``
+(src/backend.py:45) for the one thing the scorer uses it for: ``similarity`` on rows.
+All arithmetic happens in the CUDA library behind include/cassmantle_b200.h.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _lib
+from ._lib import CassMantleError, check  # noqa: F401  (re-exported)
+
+
+def _ptr(a: Optional[np.ndarray]) -> Optional[int]:
+    return None if a is None else a.ctypes.data
+
+
+class ScoringEngine:
+    def __init__(self, n_rows: int, dim: int = 300, device: int = 0) -> None:
+        self._lib = _lib.load()
+        self._h = ctypes.c_void_p()
+        check(self._lib.cm_engine_create(ctypes.byref(self._h), device, n_rows, dim))
+        self.n_rows, self.dim, self.device = int(n_rows), int(dim), int(device)
+        self._answers: Optional[Tuple[int, ...]] = None
+
+    # ---- lifecycle -------------------------------------------------------------------
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.cm_engine_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self) -> None:  # pragma: no cover - best effort
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self) -> "ScoringEngine":
+        return self
+
+    def __exit__(self, *exc) -> None:
+        self.close()
+
+    @classmethod
+    def from_vectors(cls, vectors: np.ndarray, device: int = 0,
+                     chunk_rows: int = 1 << 18) -> "ScoringEngine":
+        """Upload a host matrix (e.g. gensim's mmap'd ``wv.vectors``) chunk by chunk."""
+        if vectors.ndim != 2 or vectors.dtype != np.float32:
+            raise ValueError("vectors must be a 2-D float32 array")
+        eng = cls(vectors.shape[0], vectors.shape[1], device)
+        for lo in range(0, vectors.shape[0], chunk_rows):
+            blk = np.ascontiguousarray(vectors[lo:lo + chunk_rows])
+            check(eng._lib.cm_engine_upload_rows(eng._h, blk.ctypes.data, lo, blk.shape[0]))
+        return eng
+
+    @classmethod
+    def synthetic(cls, n_rows: int, dim: int = 300, seed: int = 0, device: int = 0) -> "ScoringEngine":
+        eng = cls(n_rows, dim, device)
+        check(eng._lib.cm_engine_fill_synthetic(eng._h, seed))
+        return eng
+
+    def download_rows(self, row0: int, n: int) -> np.ndarray:
+        out = np.empty((n, self.dim), dtype=np.float32)
+        check(self._lib.cm_engine_download_rows(self._h, out.ctypes.data, row0, n))
+        return out
+
+    @property
+    def table_ptr(self) -> int:
+        p = ctypes.c_void_p()
+        check(self._lib.cm_engine_table(self._h, ctypes.byref(p), None, None))
+        return int(p.value)
+
+    @property
+    def stream(self) -> int:
+        p = ctypes.c_void_p()
+        check(self._lib.cm_engine_stream(self._h, ctypes.byref(p)))
+        return int(p.value or 0)
+
+    def synchronize(self) -> None:
+        check(self._lib.cm_engine_synchronize(self._h))
+
+    # ---- answers ---------------------------------------------------------------------
+    def set_answers(self, rows: Sequence[int], stream: int = 0) -> None:
+        """Register the round's hidden words (table rows, -1 = unknown word)."""
+        key = tuple(int(r) for r in rows)
+        if key == self._answers:
+            return
+        arr = np.asarray(key, dtype=np.int32)
+        check(self._lib.cm_set_answers(self._h, arr.ctypes.data, arr.size, stream or None))
+        self._answers = key
+
+    def set_answers_device(self, d_rows: int, n: int, stream: int = 0) -> None:
+        check(self._lib.cm_set_answers_device(self._h, d_rows, n, stream or None))
+        self._answers = None
+
+    @property
+    def answers(self) -> Optional[Tuple[int, ...]]:
+        return self._answers
+
+    # ---- scoring ---------------------------------------------------------------------
+    def score_host(self, guess_idx: np.ndarray, guess_len: Optional[np.ndarray],
+                   answer_slot: np.ndarray, exact: Optional[np.ndarray], min_score: float,
+                   want_centi: bool = False) -> Tuple[np.ndarray, Optional[np.ndarray]]:
+        """Score a batch held in host memory; returns (fp32 scores, int32 hundredths|None)."""
+        gi = np.ascontiguousarray(guess_idx, dtype=np.int32)
+        if gi.ndim == 1:
+            gi = gi[:, None]
+        B, N = gi.shape
+        gl = (np.ones(B, dtype=np.int32) if guess_len is None
+              else np.ascontiguousarray(guess_len, dtype=np.int32))
+        sl = np.ascontiguousarray(answer_slot, dtype=np.int32)
+        ex = None if exact is None else np.ascontiguousarray(exact, dtype=np.uint8)
+        if gl.shape != (B,) or sl.shape != (B,) or (ex is not None and ex.shape != (B,)):
+            raise ValueError("guess_len / answer_slot / exact must have one entry per guess")
+        scores = np.empty(B, dtype=np.float32)
+        centi = np.empty(B, dtype=np.int32) if want_centi else None
+        if B:
+            check(self._lib.cm_score_batch_host(
+                self._h, gi.ctypes.data, gl.ctypes.data, B, max(N, 1), sl.ctypes.data, _ptr(ex),
+                ctypes.c_float(np.float32(min_score)), scores.ctypes.data, _ptr(centi)))
+        return scores, centi
+
+    def score_device(self, d_guess_idx: int, d_guess_len: int, n_guesses: int, n_slots: int,
+                     d_answer_slot: int, d_exact: int, min_score: float, d_scores: int,
+                     d_centi: int = 0, stream: int = 0) -> None:
+        """Asynchronous scoring on buffers already resident in HBM (raw device addresses)."""
+        check(self._lib.cm_score_batch_device(
+            self._h, d_guess_idx, d_guess_len, n_guesses, n_slots, d_answer_slot,
+            d_exact or None, ctypes.c_float(np.float32(min_score)), d_scores, d_centi or None,
+            stream or None))

@@ -1,0 +1,114 @@
+/*
+ * cassmantle_b200 -- C ABI of the B200-native CassMantle guess scorer.
+ *
+ * This header is the drop-in boundary for ONE path of the reference
+ * (SnowCheetos/CassMantle): Backend.compute_score / Backend.compute_scores,
+ * src/backend.py:303-317, whose arithmetic is gensim's KeyedVectors.similarity
+ * (call site src/backend.py:307) over the table loaded at src/backend.py:45.
+ * The reference is Python; the binding a maintainer adds is the ctypes stub in
+ * INTEGRATION.md (shipped here as cassmantle_b200/_lib.py).
+ *
+ * Conventions
+ *   - plain C types only; no exceptions cross the boundary; every call returns
+ *     CM_OK (0) or a negative cm_status, and cm_last_error() gives the text.
+ *   - "d_" arguments are device pointers on the engine's GPU, others are host pointers.
+ *   - a guess is N word slots: guess_idx[b*N + k] is a table row, -1 means "not in the
+ *     vocabulary" (KeyError in the reference).  guess_len[b] in [0, N] says how many
+ *     slots are used; the rest is padding.  N = 1 is the only shape the reference
+ *     itself produces; N > 1 is the mean-pool extension (gensim n_similarity).
+ *   - answers are registered once per round (cm_set_answers) and referred to by slot.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the engine's own stream).
+ */
+#ifndef CASSMANTLE_B200_H
+#define CASSMANTLE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cm_engine cm_engine;
+
+typedef enum cm_status {
+    CM_OK = 0,
+    CM_ERR_INVALID = -1,   /* bad argument (null pointer, size out of range, ...)  */
+    CM_ERR_CUDA = -2,      /* a CUDA runtime call failed; see cm_last_error()      */
+    CM_ERR_NOMEM = -3,     /* host or device allocation failed                     */
+    CM_ERR_STATE = -4      /* call order violated (e.g. scoring before answers)    */
+} cm_status;
+
+#define CM_MAX_DIM 1024        /* vector_size limit; must be a multiple of 4            */
+#define CM_MAX_ANSWERS 4096    /* answer slots per engine                               */
+#define CM_MAX_SEQ 4096        /* word slots per guess                                  */
+
+/* Text of the last error raised on the calling thread ("" if none). */
+const char *cm_last_error(void);
+
+/* Library version, "major.minor.patch". */
+const char *cm_version(void);
+
+/* ---- lifecycle ---------------------------------------------------------------------- *
+ * Replaces `self.wv = KeyedVectors.load("data/word2vec.wordvectors", mmap='r')`,
+ * src/backend.py:45: the n_rows x dim fp32 matrix becomes resident in the GPU's HBM.      */
+int cm_engine_create(cm_engine **out, int device, int64_t n_rows, int dim);
+int cm_engine_destroy(cm_engine *e);
+
+/* Copy rows [row0, row0+n) of the host matrix (row-major fp32, e.g. a slice of gensim's
+ * mmap'd `wv.vectors`) into the resident table.  Blocks until the copy is done.          */
+int cm_engine_upload_rows(cm_engine *e, const float *rows, int64_t row0, int64_t n);
+
+/* Fill the resident table with the seeded synthetic stand-in (cassmantle_b200/synth.py
+ * produces the same bits on the host).  No reference counterpart: the real weights
+ * (download_model.py:9) cannot be fetched offline.                                       */
+int cm_engine_fill_synthetic(cm_engine *e, uint32_t seed);
+
+/* Device pointer / geometry of the resident table (for tests and stream plumbing).       */
+int cm_engine_table(cm_engine *e, void **d_table, int64_t *n_rows, int *dim);
+
+/* Copy table rows back to the host (tests: compare the synthetic fill with synth.py).    */
+int cm_engine_download_rows(cm_engine *e, float *rows, int64_t row0, int64_t n);
+
+/* The engine's own stream as a cudaStream_t, and a blocking wait on it.                  */
+int cm_engine_stream(cm_engine *e, void **stream);
+int cm_engine_synchronize(cm_engine *e);
+
+/* ---- answers (src/server.py:65-72 builds them: prompt['tokens'][int(m)]) ------------- *
+ * Registers the round's hidden words as table rows (-1 = not in the vocabulary) and
+ * precomputes unitvec(row) for each, exactly once, the way gensim's similarity() would on
+ * every call.  n_answers in [1, CM_MAX_ANSWERS].  Asynchronous on `stream`.              */
+int cm_set_answers(cm_engine *e, const int32_t *answer_rows, int n_answers, void *stream);
+int cm_set_answers_device(cm_engine *e, const int32_t *d_answer_rows, int n_answers, void *stream);
+
+/* ---- the hot path --------------------------------------------------------------------- *
+ * Batched Backend.compute_score (src/backend.py:303-310) for B guesses of N slots:
+ *   exact[b] != 0                      -> 1.0        (string equality, backend.py:305)
+ *   any used slot < 0, len 0, or the
+ *   answer row < 0                     -> min_score  (KeyError, backend.py:308-309)
+ *   otherwise cos = dot(unitvec(mean of rows), unitvec(answer row))   (backend.py:307)
+ *   result = cos if cos > min_score else min_score                    (backend.py:310)
+ * d_exact may be NULL (no exact matches).  d_centi may be NULL; when given it receives
+ * floor(score * 1e4 + 0.5), the browser's (score*100).toFixed(2) in hundredths
+ * (static/script.js:300).  Asynchronous on `stream`; inputs and outputs stay in HBM.     */
+int cm_score_batch_device(cm_engine *e,
+                          const int32_t *d_guess_idx, const int32_t *d_guess_len,
+                          int n_guesses, int n_slots,
+                          const int32_t *d_answer_slot, const uint8_t *d_exact,
+                          float min_score, float *d_scores, int32_t *d_centi, void *stream);
+
+/* Same call with HOST buffers: stages the inputs to the GPU, scores, copies the results
+ * back and returns when `scores` (and `centi`, if not NULL) are valid.  This is what the
+ * Python boundary (cassmantle_b200/backend.py) calls per micro-batch.                     */
+int cm_score_batch_host(cm_engine *e,
+                        const int32_t *guess_idx, const int32_t *guess_len,
+                        int n_guesses, int n_slots,
+                        const int32_t *answer_slot, const uint8_t *exact,
+                        float min_score, float *scores, int32_t *centi);
+
+/* Number of kernels this library has launched since it was loaded (bench.py reports it). */
+int64_t cm_kernel_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CASSMANTLE_B200_H */

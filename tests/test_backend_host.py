@@ -1,0 +1,84 @@
+"""CPU tests of the host-side lowering in cassmantle_b200/backend.py.
+
+The product Backend only talks to a ScoringEngine (CUDA).  Here a stand-in engine that
+answers with the oracle is injected so the string handling -- lower(), equality before
+lookup, OOV -> -1, answer slots, result types and str() -- can be checked without a GPU.
+"""
+import asyncio
+
+import numpy as np
+
+from cassmantle_b200.backend import Backend
+from cassmantle_b200.vocab import Vocabulary
+from oracle import scorer_oracle as O
+from tests.util import dense_kat_table
+
+
+class OracleEngine:
+    """Test double with ScoringEngine's two methods used by Backend."""
+
+    def __init__(self, table):
+        self.table = table
+        self.answers = None
+        self.calls = 0
+        self.set_calls = 0
+
+    def set_answers(self, rows, stream=0):
+        self.answers = np.asarray(rows, dtype=np.int32)
+        self.set_calls += 1
+
+    def score_host(self, idx, length, slot, exact, min_score, want_centi=False):
+        self.calls += 1
+        return O.score_batch_faithful(self.table, idx, length, self.answers, slot, exact, min_score), None
+
+
+def _pair(golden, **kw):
+    table = dense_kat_table(golden)
+    keys = golden["kat"]["keys"]
+    eng = OracleEngine(table)
+    return Backend(eng, Vocabulary(keys), min_score=0.01, **kw), \
+        O.OracleBackend(O.OracleWordVectors(table, keys), 0.01), eng
+
+
+def test_compute_score_types_and_values(golden):
+    be, ref, _ = _pair(golden)
+    for c in golden["kat"]["cases"]:
+        got, want = be.compute_score(c["input"], c["answer"]), ref.compute_score(c["input"], c["answer"])
+        assert type(got) is type(want), c
+        assert str(got) == str(want) == c["str"], c
+
+
+def test_compute_scores_matches_reference_format(golden):
+    be, ref, eng = _pair(golden)
+    data = {str(i): {"input": c["input"], "answer": c["answer"]}
+            for i, c in enumerate(golden["kat"]["cases"])}
+    got = asyncio.run(be.compute_scores(data))
+    want = asyncio.run(ref.compute_scores(data))
+    assert got == want and list(got) == list(want)
+    assert eng.calls == 1                      # the whole dict is ONE device batch
+
+
+def test_answers_registered_once_per_round(golden):
+    be, _, eng = _pair(golden)
+    for _ in range(5):
+        be.compute_score("mixed", "alpha")
+        be.compute_score("mixed", "delta")
+    assert eng.set_calls == 2                  # alpha, then alpha+delta; then reused
+
+
+def test_whole_string_is_one_key_by_default(golden):
+    be, ref, _ = _pair(golden)
+    assert be.compute_score("alpha delta", "alpha") == ref.compute_score("alpha delta", "alpha") == 0.01
+
+
+def test_phrase_extension_matches_n_similarity(golden):
+    be, ref, _ = _pair(golden, phrase_guesses=True)
+    for g, a in [("alpha delta", "alpha"), ("mixed ones twin1", "quarter"), ("alpha nosuch", "alpha"),
+                 ("Alpha", "alpha"), ("delta", "alpha")]:
+        assert str(be.compute_score(g, a)) == str(ref.compute_score_phrase(g, a)), (g, a)
+
+
+def test_empty_payload(golden):
+    be, _, eng = _pair(golden)
+    assert asyncio.run(be.compute_scores({})) == {}
+    assert eng.calls == 0

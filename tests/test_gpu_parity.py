@@ -1,0 +1,292 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the oracle.
+
+Bar (stated): the exact classes are bit-exact -- 1.0 for equal strings, min_score for unknown
+words / empty guesses / cosines that do not beat the floor; cosines within COS_TOL = 2e-6
+absolute of the oracle (north_star allows 1e-3).  The synthetic table fill is bit-exact.
+"""
+import asyncio
+import ctypes
+
+import numpy as np
+import pytest
+
+from cassmantle_b200 import synth
+from oracle import c_oracle, scorer_oracle as O
+from tests.util import COS_TOL, assert_scores_match, compact_problem, dense_kat_table
+
+pytestmark = pytest.mark.gpu
+
+
+# ---------------------------------------------------------------------------------------
+# table residency
+# ---------------------------------------------------------------------------------------
+def test_synthetic_fill_is_bit_exact(small_engine, small_table):
+    for row0, n in [(0, 64), (12345, 257), (49_990, 10)]:
+        got = small_engine.download_rows(row0, n)
+        assert np.array_equal(got.view(np.uint32), small_table[row0:row0 + n].view(np.uint32))
+
+
+def test_upload_download_roundtrip():
+    from cassmantle_b200.engine import ScoringEngine
+    rng = np.random.default_rng(0)
+    vec = rng.standard_normal((1000, 300), dtype=np.float32)
+    with ScoringEngine.from_vectors(vec, chunk_rows=333) as eng:
+        assert np.array_equal(eng.download_rows(0, 1000), vec)
+        assert np.array_equal(eng.download_rows(998, 2), vec[998:])
+
+
+# ---------------------------------------------------------------------------------------
+# known answers through the reference-shaped Python boundary
+# ---------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def kat_backend(golden):
+    from cassmantle_b200.backend import Backend
+    from cassmantle_b200.engine import ScoringEngine
+    from cassmantle_b200.vocab import Vocabulary
+    table = dense_kat_table(golden)
+    eng = ScoringEngine.from_vectors(table)
+    yield Backend(eng, Vocabulary(golden["kat"]["keys"]), min_score=golden["min_score"])
+    eng.close()
+
+
+def test_kat_compute_score(kat_backend, golden):
+    for c in golden["kat"]["cases"]:
+        s = kat_backend.compute_score(c["input"], c["answer"])
+        assert (not isinstance(s, np.floating)) == c["is_python_float"], c
+        if c["is_python_float"]:
+            assert str(s) == c["str"], c
+        else:
+            assert abs(float(s) - float.fromhex(c["f32_hex"])) <= COS_TOL, c
+
+
+def test_kat_exact_strings(kat_backend):
+    data = {"3": {"input": "Alpha", "answer": "alpha"},
+            "7": {"input": "alpha", "answer": "delta"},
+            "9": {"input": "Beta", "answer": "dELTA"},
+            "1": {"input": "qqq", "answer": "delta"},
+            "2": {"input": "alpha", "answer": "gamma"},
+            "4": {"input": "void", "answer": "alpha"}}
+    out = asyncio.run(kat_backend.compute_scores(data))
+    assert out == {"3": "1.0", "7": "0.6", "9": "0.8", "1": "0.01", "2": "0.01", "4": "0.01"}
+    assert list(out) == ["3", "7", "9", "1", "2", "4"]
+
+
+def test_kat_fp64_norm_path(kat_backend):
+    # fp32 squares of 1e-20 underflow and of 1e20 overflow; gensim's double nrm2 does not care
+    assert abs(float(kat_backend.compute_score("tiny", "huge")) - 1.0) <= COS_TOL
+    assert abs(float(kat_backend.compute_score("ones", "quarter")) - 0.5) <= COS_TOL
+
+
+def test_golden_synth_cases(small_engine, golden):
+    cases = golden["synth"]["cases"]
+    for n_slots in (1, 4, 16):
+        sel = [c for c in cases if len(c["rows"]) == n_slots]
+        idx = np.asarray([c["rows"] for c in sel], dtype=np.int32)
+        ln = np.asarray([c["len"] for c in sel], dtype=np.int32)
+        ans = sorted({c["answer_row"] for c in sel})
+        slot = np.asarray([ans.index(c["answer_row"]) for c in sel], dtype=np.int32)
+        ex = np.asarray([c["exact"] for c in sel], dtype=np.uint8)
+        want = np.asarray([float.fromhex(c["f32_hex"]) for c in sel], dtype=np.float32)
+        small_engine.set_answers(ans)
+        got, _ = small_engine.score_host(idx, ln, slot, ex, 0.01)
+        assert_scores_match(got, want, 0.01)
+
+
+# ---------------------------------------------------------------------------------------
+# seeded batches against the numpy oracle
+# ---------------------------------------------------------------------------------------
+@pytest.mark.parametrize("B,N,ragged", [
+    (1, 1, False), (7, 1, False), (64, 1, False), (512, 8, False), (513, 8, True),
+    (4096, 1, False), (4096, 16, False), (1000, 16, True), (300, 33, True), (129, 64, True),
+    (50, 100, True),
+])
+def test_batch_matches_oracle(small_engine, small_table, B, N, ragged):
+    idx, ln, ans, slot, ex = synth.make_guess_batch(B, N, 50_000, n_answers=3, seed=B * 131 + N,
+                                                    ragged=ragged)
+    small_engine.set_answers(ans)
+    got, centi = small_engine.score_host(idx, ln, slot, ex, 0.01, want_centi=True)
+    want = O.score_batch_faithful(small_table, idx, ln, ans, slot, ex, 0.01) if B * N <= 70_000 \
+        else c_oracle.score_batch(small_table, idx, ln, ans, slot, ex, 0.01, threads=4)
+    assert_scores_match(got, want, 0.01)
+    assert np.all(got[ex.astype(bool)] == np.float32(1.0))
+    # hundredths of a percent, as the browser rounds them (static/script.js:300); the stated
+    # rounding boundary: score*1e4 within 2e-3 of a half-integer may round either way
+    x = got.astype(np.float64) * 1e4
+    safe = np.abs((x % 1.0) - 0.5) > 2e-3
+    floor32 = np.float32(0.01)
+    strs = ["1.0" if ex[b] else (str(got[b]) if got[b] > floor32 else "0.01") for b in range(B)]
+    want_centi = np.asarray([O.centi_score(s) for s in strs])
+    assert np.array_equal(centi[safe], want_centi[safe])
+
+
+def test_device_entry_point_equals_host_entry_point(small_engine):
+    import torch
+    B, N = 2048, 16
+    idx, ln, ans, slot, ex = synth.make_guess_batch(B, N, 50_000, 2, seed=5, ragged=True)
+    small_engine.set_answers(ans)
+    want, want_c = small_engine.score_host(idx, ln, slot, ex, 0.01, want_centi=True)
+    dev = torch.device("cuda:0")
+    t = [torch.from_numpy(a).to(dev) for a in (idx, ln, slot, ex)]
+    out = torch.empty(B, dtype=torch.float32, device=dev)
+    cen = torch.empty(B, dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    small_engine.score_device(t[0].data_ptr(), t[1].data_ptr(), B, N, t[2].data_ptr(),
+                              t[3].data_ptr(), 0.01, out.data_ptr(), cen.data_ptr(), stream=st)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(cen.cpu().numpy(), want_c)
+    # exact == NULL means "no exact matches"
+    small_engine.score_device(t[0].data_ptr(), t[1].data_ptr(), B, N, t[2].data_ptr(), 0, 0.01,
+                              out.data_ptr(), 0, stream=st)
+    torch.cuda.synchronize()
+    want2, _ = small_engine.score_host(idx, ln, slot, None, 0.01)
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), want2.view(np.uint32))
+
+
+# ---------------------------------------------------------------------------------------
+# edge cases the reference's semantics define
+# ---------------------------------------------------------------------------------------
+def test_edge_cases(small_engine, small_table):
+    V = 50_000
+    idx = np.array([[5, -1, 7, 8],          # OOV inside the used part        -> floor
+                    [5, 6, -1, -1],         # OOV only in the padding         -> cosine
+                    [-1, -1, -1, -1],       # empty guess                     -> floor
+                    [V, 1, 2, 3],           # row beyond the table = unknown  -> floor
+                    [9, 9, 9, 9],           # the answer row itself           -> ~1
+                    [1, 2, 3, 4],           # unknown answer                  -> floor
+                    [1, 2, 3, 4],           # slot out of range               -> floor
+                    [1, 2, 3, 4]],          # exact flag wins over everything -> 1.0
+                   dtype=np.int32)
+    ln = np.array([4, 2, 0, 4, 4, 4, 4, 4], dtype=np.int32)
+    ans = np.array([9, -1], dtype=np.int32)
+    slot = np.array([0, 0, 0, 0, 0, 1, 7, 1], dtype=np.int32)
+    ex = np.array([0, 0, 0, 0, 0, 0, 0, 1], dtype=np.uint8)
+    small_engine.set_answers(ans)
+    got, _ = small_engine.score_host(idx, ln, slot, ex, 0.01)
+    f = np.float32(0.01)
+    assert got[0] == f and got[2] == f and got[3] == f and got[5] == f and got[6] == f
+    assert got[7] == np.float32(1.0)
+    assert abs(float(got[4]) - 1.0) <= COS_TOL
+    want1 = O.n_similarity(small_table, [5, 6], [9])
+    assert abs(float(got[1]) - max(0.01, float(want1))) <= COS_TOL
+    # empty batch is a no-op
+    e, _ = small_engine.score_host(np.zeros((0, 4), np.int32), np.zeros(0, np.int32),
+                                   np.zeros(0, np.int32), None, 0.01)
+    assert e.shape == (0,)
+
+
+def test_nan_and_zero_rows_floor():
+    from cassmantle_b200.engine import ScoringEngine
+    vec = np.ones((4, 300), dtype=np.float32)
+    vec[1] = 0.0
+    vec[2, 7] = np.nan
+    vec[3] = -1.0
+    with ScoringEngine.from_vectors(vec) as eng:
+        eng.set_answers([0])
+        got, _ = eng.score_host(np.array([[0], [1], [2], [3]], np.int32), None,
+                                np.zeros(4, np.int32), None, 0.01)
+    assert abs(float(got[0]) - 1.0) <= COS_TOL
+    assert got[1] == np.float32(0.01)      # zero norm: unitvec leaves it, cos 0
+    assert got[2] == np.float32(0.01)      # max(min_score, nan) is min_score in Python
+    assert got[3] == np.float32(0.01)      # anti-parallel
+
+
+def test_min_score_is_a_parameter(small_engine, small_table):
+    idx, ln, ans, slot, ex = synth.make_guess_batch(512, 1, 50_000, 2, seed=77)
+    small_engine.set_answers(ans)
+    for ms in (0.1, 0.01, 0.5, -1.0):
+        got, _ = small_engine.score_host(idx, ln, slot, ex, ms)
+        want = O.score_batch_faithful(small_table, idx, ln, ans, slot, ex, ms)
+        assert_scores_match(got, want, ms)
+
+
+def test_many_answers(small_engine, small_table):
+    from cassmantle_b200._lib import CM_MAX_ANSWERS
+    rng = np.random.default_rng(3)
+    ans = rng.integers(0, 50_000, CM_MAX_ANSWERS).astype(np.int32)
+    ans[5] = -1
+    idx = rng.integers(0, 50_000, (3000, 1)).astype(np.int32)
+    slot = rng.integers(0, CM_MAX_ANSWERS, 3000).astype(np.int32)
+    small_engine.set_answers(ans)
+    got, _ = small_engine.score_host(idx, None, slot, None, 0.01)
+    want = c_oracle.score_batch(small_table, idx, np.ones(3000, np.int32), ans, slot, None, 0.01)
+    assert_scores_match(got, want, 0.01)
+
+
+def test_other_dims():
+    """vector_size is a table property, not a constant: any multiple of 4 up to 1024."""
+    from cassmantle_b200.engine import ScoringEngine
+    rng = np.random.default_rng(11)
+    for dim in (4, 64, 128, 132, 512, 1024):
+        vec = rng.standard_normal((500, dim), dtype=np.float32)
+        idx = rng.integers(0, 500, (200, 5)).astype(np.int32)
+        ln = rng.integers(1, 6, 200).astype(np.int32)
+        ans = np.array([3, 4], np.int32)
+        slot = rng.integers(0, 2, 200).astype(np.int32)
+        with ScoringEngine.from_vectors(vec) as eng:
+            eng.set_answers(ans)
+            got, _ = eng.score_host(idx, ln, slot, None, 0.01)
+        want = O.score_batch_faithful(vec, idx, ln, ans, slot, None, 0.01)
+        assert_scores_match(got, want, 0.01)
+
+
+def test_abi_rejects_bad_arguments(small_engine):
+    from cassmantle_b200 import _lib
+    lib = _lib.load()
+    h = small_engine._h
+    one = np.zeros(1, np.int32)
+    f = np.zeros(1, np.float32)
+    assert lib.cm_score_batch_host(h, one.ctypes.data, one.ctypes.data, 1, 0, one.ctypes.data,
+                                   None, 0.01, f.ctypes.data, None) == -1
+    assert lib.cm_score_batch_host(h, None, one.ctypes.data, 1, 1, one.ctypes.data,
+                                   None, 0.01, f.ctypes.data, None) == -1
+    assert lib.cm_set_answers(h, one.ctypes.data, 0, None) == -1
+    assert lib.cm_set_answers(h, one.ctypes.data, _lib.CM_MAX_ANSWERS + 1, None) == -1
+    assert lib.cm_engine_upload_rows(h, f.ctypes.data, 49_999, 2) == -1
+    assert b"outside" in lib.cm_last_error()
+    h2 = ctypes.c_void_p()
+    assert lib.cm_engine_create(ctypes.byref(h2), 99, 10, 300) == -1
+
+
+# ---------------------------------------------------------------------------------------
+# BASELINE.json's full sizes: size-independent properties + a sampled oracle check
+# ---------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def full_engine():
+    from cassmantle_b200.engine import ScoringEngine
+    eng = ScoringEngine.synthetic(synth.FULL_ROWS, 300, seed=0, device=0)
+    yield eng
+    eng.close()
+
+
+@pytest.mark.parametrize("B,N", [(512, 8), (4096, 16), (65536, 16), (16384, 64), (65536, 1)])
+def test_full_size_configs(full_engine, B, N):
+    V = synth.FULL_ROWS
+    idx, ln, ans, slot, ex = synth.make_guess_batch(B, N, V, n_answers=3, seed=B + N)
+    full_engine.set_answers(ans)
+    got, _ = full_engine.score_host(idx, ln, slot, ex, 0.01)
+    again, _ = full_engine.score_host(idx, ln, slot, ex, 0.01)
+    assert np.array_equal(got.view(np.uint32), again.view(np.uint32))          # idempotent
+    assert np.all(got >= np.float32(0.01)) and np.all(got <= np.float32(1.0 + 1e-6))
+    assert np.all(got[ex.astype(bool)] == np.float32(1.0))
+    # a guess made only of the answer's own row scores ~1; doubling a guess' words (same mean
+    # direction) leaves its score unchanged to rounding
+    if N >= 2:
+        half = N // 2
+        dup = idx.copy()
+        dup[:, half:2 * half] = dup[:, :half]
+        dl = np.full(B, 2 * half, np.int32)
+        hl = np.full(B, half, np.int32)
+        a, _ = full_engine.score_host(dup, dl, slot, None, 0.01)
+        b, _ = full_engine.score_host(idx, hl, slot, None, 0.01)
+        # a guess that has an OOV word in its first half floors in both; one with the OOV word only
+        # in the second half floors in neither after the overwrite
+        assert np.abs(a - b).max() <= 4e-6
+    own = np.repeat(ans[slot][:, None], N, axis=1).astype(np.int32)
+    s, _ = full_engine.score_host(own, ln, slot, None, 0.01)
+    assert np.abs(s - 1.0).max() <= COS_TOL
+    # sampled oracle check on the rows this batch touches (the host never builds 3.6 GB)
+    pick = np.random.default_rng(0).choice(B, size=min(B, 1024), replace=False)
+    table, ridx, rans = compact_problem(idx[pick], ans)
+    want = c_oracle.score_batch(table, ridx, ln[pick], rans, slot[pick], ex[pick], 0.01, threads=4)
+    assert_scores_match(got[pick], want, 0.01)
