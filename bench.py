@@ -44,6 +44,7 @@ B, N = 4096, 16
 N_ANSWERS = 2
 MIN_SCORE = 0.01
 RING = 64                      # distinct batches cycled through (64 x 79 MB of rows)
+OVERLAP = 1                    # CM_SCORE_OVERLAP_PREVIOUS: the ring's batches are independent
 BYTES_PER_GUESS = N * (D * 4 + 4) + 8      # N rows + N indices + len/slot + score
 METRIC = "guesses_scored_per_sec"
 UNIT = "guesses/s"
@@ -160,7 +161,7 @@ class ClockSampler(threading.Thread):
         self.index, self.period = index, period
         self.samples, self.reasons = [], set()
         self.sm_max = None
-        self._stop = threading.Event()
+        self._halt = threading.Event()
         self.ok = False
         try:
             import pynvml
@@ -176,7 +177,7 @@ class ClockSampler(threading.Thread):
         if not self.ok:
             return
         nv = self.nv
-        while not self._stop.is_set():
+        while not self._halt.is_set():
             try:
                 self.samples.append(int(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
                 mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
@@ -185,10 +186,10 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(self.period)
+            self._halt.wait(self.period)
 
     def stop(self):
-        self._stop.set()
+        self._halt.set()
         if self.is_alive():
             self.join()
         med = float(np.median(self.samples)) if self.samples else None
@@ -255,13 +256,15 @@ def run_own(args) -> None:
     d_scores = torch.empty(B, dtype=torch.float32, device=dev)
     gathered = torch.empty(world * B, dtype=torch.float32, device=dev) if world > 1 else None
     h_scores = torch.empty(B, dtype=torch.float32).pin_memory()
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream(device=dev)      # every kernel, event and collective below uses it
+    torch.cuda.set_stream(stream)
     st = stream.cuda_stream
+    assert st != 0
 
     def step_device(i: int) -> None:
         t = d_ring[i % RING]
         eng.score_device(t[0].data_ptr(), t[1].data_ptr(), B, N, t[2].data_ptr(), t[3].data_ptr(),
-                         MIN_SCORE, d_scores.data_ptr(), 0, stream=st)
+                         MIN_SCORE, d_scores.data_ptr(), 0, stream=st, flags=OVERLAP)
         if world > 1:        # north_star: per-guess scores are all-gathered over NVLink
             dist.all_gather_into_tensor(gathered, d_scores)
 
@@ -315,13 +318,13 @@ def run_own(args) -> None:
     fn, h, out_p = lib.cm_score_batch_device, eng._h, d_scores.data_ptr()
     for i in range(50):
         p = t_ring[i % RING]
-        fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, st)
+        fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
     torch.cuda.synchronize()
     r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     r0.record(stream)
     for i in range(n_roof):
         p = t_ring[i % RING]
-        fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, st)
+        fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
     r1.record(stream)
     torch.cuda.synchronize()
     kern_us = r0.elapsed_time(r1) * 1e3 / n_roof

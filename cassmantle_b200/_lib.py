@@ -19,6 +19,7 @@ CM_OK = 0
 CM_MAX_DIM = 1024
 CM_MAX_ANSWERS = 4096
 CM_MAX_SEQ = 4096
+CM_SCORE_OVERLAP_PREVIOUS = 0x1
 
 
 class CassMantleError(RuntimeError):
@@ -46,7 +47,7 @@ _SIGNATURES = {
     "cm_set_answers": (_c.c_int, [_P, _P, _c.c_int, _P]),
     "cm_set_answers_device": (_c.c_int, [_P, _P, _c.c_int, _P]),
     "cm_score_batch_device": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _P, _P, _c.c_float,
-                                         _P, _P, _P]),
+                                         _P, _P, _c.c_uint32, _P]),
     "cm_score_batch_host": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _P, _P, _c.c_float,
                                        _P, _P]),
 }

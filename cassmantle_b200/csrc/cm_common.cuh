@@ -27,6 +27,14 @@ __device__ __forceinline__ float4 ld_stream_f4(const float4 *p) {
     return v;
 }
 
+// Programmatic dependent launch (PDL) controls; both are no-ops for a plain launch.
+__device__ __forceinline__ void pdl_launch_dependents() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(kFullMask, v, o);

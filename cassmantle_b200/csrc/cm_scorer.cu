@@ -14,6 +14,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -55,7 +56,6 @@ struct DeviceGuard {
 };
 
 constexpr int kWarpsPerCta = 8;
-constexpr int kRowsInFlight = 4;   // table rows a warp requests before it starts adding
 
 // --------------------------------------------------------------------------------------
 // Synthetic table fill -- bit-identical to cassmantle_b200/synth.py: table_rows().
@@ -89,12 +89,19 @@ cm_synth_fill_kernel(float *__restrict__ table, int64_t n_rows, int dim, uint32_
 }
 
 // --------------------------------------------------------------------------------------
-// unitvec() in registers.  Lane `l` of a warp holds float4 vectors l, l+32, ... of one row.
-// gensim matutils.unitvec: veclen = dnrm2(v); v * (1/veclen) in fp64, cast back to fp32;
-// a zero vector is returned unchanged.
+// unitvec() in registers.  A group of LPG lanes (LPG = 32, 16 or 8) holds one vector: lane
+// `sub` of the group owns float4 elements sub, sub+LPG, ...  gensim matutils.unitvec:
+// veclen = dnrm2(v); v * (1/veclen) in fp64, cast back to fp32; a zero vector is unchanged.
 // --------------------------------------------------------------------------------------
-template <int VPL>
-__device__ __forceinline__ void warp_unitvec(float4 (&m)[VPL]) {
+template <int LPG, typename T>
+__device__ __forceinline__ T group_sum(T v) {
+#pragma unroll
+    for (int o = LPG / 2; o > 0; o >>= 1) v += __shfl_xor_sync(cm::kFullMask, v, o);
+    return v;
+}
+
+template <int VPL, int LPG>
+__device__ __forceinline__ void group_unitvec(float4 (&m)[VPL]) {
     double ss = 0.0;
 #pragma unroll
     for (int v = 0; v < VPL; ++v) {
@@ -103,7 +110,7 @@ __device__ __forceinline__ void warp_unitvec(float4 (&m)[VPL]) {
         ss = fma((double)m[v].z, (double)m[v].z, ss);
         ss = fma((double)m[v].w, (double)m[v].w, ss);
     }
-    ss = cm::warp_sum(ss);
+    ss = group_sum<LPG>(ss);
     if (ss > 0.0) {
         const double inv = 1.0 / sqrt(ss);
 #pragma unroll
@@ -134,7 +141,7 @@ cm_answer_unit_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
         const int j = lane + 32 * v;
         m[v] = (in_vocab && j < dim4) ? __ldg(src + j) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    warp_unitvec<VPL>(m);
+    group_unitvec<VPL, 32>(m);
     float4 *dst = reinterpret_cast<float4 *>(ans_unit) + (size_t)a * dim4;
 #pragma unroll
     for (int v = 0; v < VPL; ++v) {
@@ -144,111 +151,139 @@ cm_answer_unit_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
 }
 
 // --------------------------------------------------------------------------------------
-// The scoring kernel: one warp per guess.
-//   gather N rows (streaming 16-byte loads, kRowsInFlight rows requested at a time)
-//   -> fp32 in-order sum -> / N -> unitvec (fp64 norm) -> fp32 dot with the answer's unit
-//   vector -> floor at min_score -> fp32 score (+ optional hundredths of a percent).
+// The scoring kernel.  A group of LPG lanes owns one guess, so a warp scores 32/LPG guesses
+// side by side (LPG = 32 for phrases, 8 for the reference's one-word guesses, where the
+// per-guess latency chain, not bandwidth, is what has to be hidden).
+//   phase 0  every independent metadata load at once: exact flag, length, answer slot,
+//            the first LPG word indices (speculatively, bounded by n_slots)
+//   phase 1  gather: R rows requested per round with 16-byte loads, then added in word
+//            order in fp32 (numpy mean(axis=0) is a running fp32 sum)
+//   phase 2  / N, unitvec through an fp64 norm, fp32 dot with the answer's unit vector,
+//            floor at min_score, optional hundredths of a percent
 // --------------------------------------------------------------------------------------
-template <int VPL>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
                 const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
                 int n_guesses, int n_slots,
                 const float *__restrict__ ans_unit, const int32_t *__restrict__ ans_rows,
                 int n_answers, const int32_t *__restrict__ answer_slot,
                 const uint8_t *__restrict__ exact, float min_score,
-                float *__restrict__ scores, int32_t *__restrict__ centi) {
+                float *__restrict__ scores, int32_t *__restrict__ centi, uint32_t flags) {
+    constexpr int G = 32 / LPG;
+    // Programmatic dependent launch: let the next launch on the stream start scheduling now,
+    // and unless the caller vouched for the inputs (CM_SCORE_OVERLAP_PREVIOUS) wait for the
+    // previous kernel on the stream before reading anything.
+    cm::pdl_launch_dependents();
+    const bool overlap = (flags & CM_SCORE_OVERLAP_PREVIOUS) != 0u;
+    if (!overlap) cm::pdl_wait();
     const int lane = threadIdx.x & 31;
-    const int b = blockIdx.x * kWarpsPerCta + (threadIdx.x >> 5);
-    if (b >= n_guesses) return;
+    const int sub = lane & (LPG - 1);
+    const int grp_base = lane & ~(LPG - 1);
+    const int warp = blockIdx.x * (THREADS / 32) + (threadIdx.x >> 5);
+    const int b_raw = warp * G + lane / LPG;
+    if (warp * G >= n_guesses) return;                      // whole warp out of range
+    const bool have = b_raw < n_guesses;
+    const int b = have ? b_raw : n_guesses - 1;             // keep every lane's loads in bounds
 
-    float result;
-    if (exact != nullptr && exact[b] != 0) {
-        result = 1.0f;                                     // src/backend.py:305
-    } else {
-        int n = guess_len[b];
-        n = n < 0 ? 0 : (n > n_slots ? n_slots : n);
-        const int slot = answer_slot[b];
-        const int32_t *gi = guess_idx + (size_t)b * n_slots;
+    // ---- phase 0: independent loads, one DRAM round trip ---------------------------------
+    const int32_t *gi = guess_idx + (size_t)b * n_slots;
+    const bool is_exact = (exact != nullptr) && (exact[b] != 0);
+    int n = guess_len[b];
+    const int slot = answer_slot[b];
+    int32_t mine = (sub < n_slots) ? gi[sub] : -1;
+    n = n < 0 ? 0 : (n > n_slots ? n_slots : n);
+    const bool slot_ok = slot >= 0 && slot < n_answers;
 
-        // KeyError scan: any used slot outside the table, an empty guess, or an unknown answer.
-        bool bad = false;
-        for (int c = lane; c < n; c += 32) {
-            const int32_t r = gi[c];
-            bad |= (r < 0) || ((int64_t)r >= n_rows);
-        }
-        bad = __any_sync(cm::kFullMask, bad) || n == 0 || slot < 0 || slot >= n_answers;
-        if (!bad) {
-            const int32_t ar = ans_rows[slot];
-            bad = ar < 0 || (int64_t)ar >= n_rows;
-        }
+    // KeyError scan: a used slot outside the table, an empty guess, or an unknown answer.
+    bool bad = (sub < n) && (mine < 0 || (int64_t)mine >= n_rows);
+    for (int c = LPG + sub; c < n; c += LPG) {
+        const int32_t r = gi[c];
+        bad |= (r < 0) || ((int64_t)r >= n_rows);
+    }
+    const unsigned gmask = (LPG == 32) ? cm::kFullMask : (((1u << LPG) - 1u) << grp_base);
+    bad = (__ballot_sync(cm::kFullMask, bad) & gmask) != 0u;
+    bad = bad || n == 0 || !slot_ok;
+    const bool active = have && !is_exact && !bad;
+    const int n_live = active ? n : 0;
+    const int n_max = (G == 1) ? n_live : __reduce_max_sync(cm::kFullMask, n_live);
 
-        if (bad) {
-            result = min_score;                            // src/backend.py:308-310
-        } else {
-            float4 acc[VPL];
+    float4 acc[VPL];
 #pragma unroll
-            for (int v = 0; v < VPL; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int v = 0; v < VPL; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 *table4 = reinterpret_cast<const float4 *>(table);
 
-            for (int c = 0; c < n; c += 32) {
-                const int m = min(32, n - c);
-                const int32_t mine = (lane < m) ? gi[c + lane] : 0;
-                for (int k = 0; k < m; k += kRowsInFlight) {
-                    float4 buf[kRowsInFlight][VPL];
+    // ---- phase 1: gather ------------------------------------------------------------------
+    for (int c = 0; c < n_max; c += LPG) {
+        if (c > 0) mine = (c + sub < n_live) ? gi[c + sub] : 0;
+        const int m = min(LPG, n_max - c);
+        for (int k = 0; k < m; k += R) {
+            float4 buf[R][VPL];
 #pragma unroll
-                    for (int i = 0; i < kRowsInFlight; ++i) {
-                        const int32_t r = __shfl_sync(cm::kFullMask, mine, (k + i) & 31);
-                        const bool live = (k + i) < m;
-                        const float4 *src = reinterpret_cast<const float4 *>(table) + (size_t)r * dim4;
-#pragma unroll
-                        for (int v = 0; v < VPL; ++v) {
-                            const int j = lane + 32 * v;
-                            buf[i][v] = (live && j < dim4) ? cm::ld_stream_f4(src + j)
-                                                           : make_float4(0.f, 0.f, 0.f, 0.f);
-                        }
-                    }
-#pragma unroll
-                    for (int i = 0; i < kRowsInFlight; ++i) {
-#pragma unroll
-                        for (int v = 0; v < VPL; ++v) {          // word order, like mean(axis=0)
-                            acc[v].x += buf[i][v].x;
-                            acc[v].y += buf[i][v].y;
-                            acc[v].z += buf[i][v].z;
-                            acc[v].w += buf[i][v].w;
-                        }
-                    }
-                }
-            }
-            if (n > 1) {
-                const float fn = (float)n;
+            for (int i = 0; i < R; ++i) {
+                const int32_t r = __shfl_sync(cm::kFullMask, mine, grp_base + ((k + i) & (LPG - 1)));
+                const bool live = (k + i) < m && (c + k + i) < n_live;
+                const float4 *src = table4 + (size_t)(live ? r : 0) * dim4;
 #pragma unroll
                 for (int v = 0; v < VPL; ++v) {
-                    acc[v].x = __fdiv_rn(acc[v].x, fn);
-                    acc[v].y = __fdiv_rn(acc[v].y, fn);
-                    acc[v].z = __fdiv_rn(acc[v].z, fn);
-                    acc[v].w = __fdiv_rn(acc[v].w, fn);
+                    const int j = sub + LPG * v;
+                    if (live && j < dim4) buf[i][v] = STREAM ? cm::ld_stream_f4(src + j) : __ldg(src + j);
+                    else buf[i][v] = make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             }
-            warp_unitvec<VPL>(acc);
-
-            const float4 *u = reinterpret_cast<const float4 *>(ans_unit) + (size_t)slot * dim4;
-            float p = 0.f;
 #pragma unroll
-            for (int v = 0; v < VPL; ++v) {
-                const int j = lane + 32 * v;
-                if (j < dim4) {
-                    const float4 w = __ldg(u + j);
-                    p = fmaf(acc[v].x, w.x, p);
-                    p = fmaf(acc[v].y, w.y, p);
-                    p = fmaf(acc[v].z, w.z, p);
-                    p = fmaf(acc[v].w, w.w, p);
+            for (int i = 0; i < R; ++i) {
+#pragma unroll
+                for (int v = 0; v < VPL; ++v) {              // word order, like mean(axis=0)
+                    acc[v].x += buf[i][v].x;
+                    acc[v].y += buf[i][v].y;
+                    acc[v].z += buf[i][v].z;
+                    acc[v].w += buf[i][v].w;
                 }
             }
-            p = cm::warp_sum(p);
-            result = (p > min_score) ? p : min_score;      // max(min_score, score): NaN -> min
         }
     }
-    if (lane == 0) {
+
+    // ---- phase 2: mean, unitvec, dot, floor -----------------------------------------------
+    // The answers (ans_rows / ans_unit) and the outputs are the only things an overlapped
+    // launch shares with its predecessor: from here on the previous kernel must be complete.
+    if (overlap) cm::pdl_wait();
+    {
+        const int32_t ar = slot_ok ? ans_rows[slot] : -1;     // unknown answer = KeyError too
+        bad = bad || ar < 0 || (int64_t)ar >= n_rows;
+    }
+    if (n_max > 1) {                                         // warp-uniform; x / 1 is exact anyway
+        const float fn = (float)(n_live > 1 ? n_live : 1);
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+            acc[v].x = __fdiv_rn(acc[v].x, fn);
+            acc[v].y = __fdiv_rn(acc[v].y, fn);
+            acc[v].z = __fdiv_rn(acc[v].z, fn);
+            acc[v].w = __fdiv_rn(acc[v].w, fn);
+        }
+    }
+    float p = 0.f;
+    if (n_max > 0) {                                         // warp-uniform
+        group_unitvec<VPL, LPG>(acc);
+        const float4 *u = reinterpret_cast<const float4 *>(ans_unit) + (size_t)(active ? slot : 0) * dim4;
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+            const int j = sub + LPG * v;
+            if (j < dim4) {
+                const float4 w = u[j];       // plain load: written by the answer kernel, maybe just now
+                p = fmaf(acc[v].x, w.x, p);
+                p = fmaf(acc[v].y, w.y, p);
+                p = fmaf(acc[v].z, w.z, p);
+                p = fmaf(acc[v].w, w.w, p);
+            }
+        }
+        p = group_sum<LPG>(p);
+    }
+    float result;
+    if (is_exact) result = 1.0f;                             // src/backend.py:305
+    else if (bad) result = min_score;                        // src/backend.py:308-310
+    else result = (p > min_score) ? p : min_score;           // max(min_score, score): NaN -> min
+    if (have && sub == 0) {
         scores[b] = result;
         if (centi != nullptr) centi[b] = (int32_t)floor((double)result * 10000.0 + 0.5);
     }
@@ -274,15 +309,69 @@ struct cm_engine {
 
 namespace {
 
+// Kernel variants.  `CM_SCORE_VARIANT` (environment, read once) forces one for tuning runs.
+//   wide   : 32 lanes per guess, R rows per round   -- phrases (N >= 3) and any table width
+//   narrow : 8 lanes per guess, 4 guesses per warp   -- one- and two-word guesses, dim 300 only
+template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS>
+void launch_variant(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
+                    const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
+                    int32_t *centi, uint32_t flags, cudaStream_t st) {
+    constexpr int per_cta = (THREADS / 32) * (32 / LPG);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((B + per_cta - 1) / per_cta));
+    cfg.blockDim = dim3(THREADS);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, cm_score_kernel<VPL, LPG, R, STREAM, THREADS, MIN_BLOCKS>,
+                       (const float *)e->d_table, e->n_rows, e->dim / 4, gi, gl, B, N,
+                       (const float *)e->d_ans_unit, (const int32_t *)e->d_ans_rows, e->n_answers,
+                       slot, exact, min_score, scores, centi, flags);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+}
+
+int forced_variant() {
+    static const int v = [] {
+        const char *s = getenv("CM_SCORE_VARIANT");
+        return s ? atoi(s) : 0;
+    }();
+    return v;
+}
+
 template <int VPL>
 void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
                   const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
-                  int32_t *centi, cudaStream_t st) {
-    const int grid = (B + kWarpsPerCta - 1) / kWarpsPerCta;
-    cm_score_kernel<VPL><<<grid, kWarpsPerCta * 32, 0, st>>>(
-        e->d_table, e->n_rows, e->dim / 4, gi, gl, B, N, e->d_ans_unit, e->d_ans_rows,
-        e->n_answers, slot, exact, min_score, scores, centi);
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+                  int32_t *centi, uint32_t flags, cudaStream_t st) {
+#define CM_V(LPG, R, STREAM, THREADS, MINB, VP) \
+    launch_variant<VP, LPG, R, STREAM, THREADS, MINB>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st)
+    if constexpr (VPL == 3) {
+        if (e->dim == 300) {
+            int variant = forced_variant();
+            if (variant == 0) variant = (N <= 2) ? 7 : 8;
+            switch (variant) {
+                case 1: CM_V(32, 4, true, 128, 7, 3); return;
+                case 2: CM_V(32, 8, true, 128, 4, 3); return;
+                case 3: CM_V(8, 1, false, 128, 5, 10); return;
+                case 4: CM_V(8, 2, false, 128, 4, 10); return;
+                case 5: CM_V(16, 1, false, 128, 7, 5); return;
+                case 6: CM_V(16, 2, false, 128, 6, 5); return;
+                case 7: CM_V(8, 1, true, 128, 5, 10); return;
+                case 8: CM_V(32, 2, true, 128, 8, 3); return;
+                case 9: CM_V(32, 4, true, 256, 3, 3); return;
+                case 10: CM_V(32, 3, true, 128, 7, 3); return;
+                case 11: CM_V(32, 3, true, 256, 3, 3); return;
+                case 12: CM_V(32, 4, true, 128, 6, 3); return;
+                case 13: CM_V(32, 4, true, 256, 1, 3); return;
+                case 14: CM_V(32, 3, true, 128, 8, 3); return;
+                default: break;
+            }
+        }
+    }
+    CM_V(32, 4, true, 256, 1, VPL);
+#undef CM_V
 }
 
 template <int VPL>
@@ -462,7 +551,7 @@ int cm_set_answers_device(cm_engine *e, const int32_t *d_answer_rows, int n_answ
     if (n_answers < 1 || n_answers > CM_MAX_ANSWERS)
         return fail(CM_ERR_INVALID, "n_answers %d outside [1, %d]", n_answers, CM_MAX_ANSWERS);
     DeviceGuard guard(e->device);
-    cudaStream_t st = stream ? (cudaStream_t)stream : e->stream;
+    cudaStream_t st = (cudaStream_t)stream;
     if (d_answer_rows != e->d_ans_rows)
         CM_CUDA(cudaMemcpyAsync(e->d_ans_rows, d_answer_rows, (size_t)n_answers * sizeof(int32_t),
                                 cudaMemcpyDeviceToDevice, st));
@@ -480,7 +569,7 @@ int cm_set_answers(cm_engine *e, const int32_t *answer_rows, int n_answers, void
     if (n_answers < 1 || n_answers > CM_MAX_ANSWERS)
         return fail(CM_ERR_INVALID, "n_answers %d outside [1, %d]", n_answers, CM_MAX_ANSWERS);
     DeviceGuard guard(e->device);
-    cudaStream_t st = stream ? (cudaStream_t)stream : e->stream;
+    cudaStream_t st = (cudaStream_t)stream;
     // pageable source: the runtime stages it before returning, so the caller's buffer is free
     CM_CUDA(cudaMemcpyAsync(e->d_ans_rows, answer_rows, (size_t)n_answers * sizeof(int32_t),
                             cudaMemcpyHostToDevice, st));
@@ -490,7 +579,7 @@ int cm_set_answers(cm_engine *e, const int32_t *answer_rows, int n_answers, void
 int cm_score_batch_device(cm_engine *e, const int32_t *d_guess_idx, const int32_t *d_guess_len,
                           int n_guesses, int n_slots, const int32_t *d_answer_slot,
                           const uint8_t *d_exact, float min_score, float *d_scores,
-                          int32_t *d_centi, void *stream) {
+                          int32_t *d_centi, uint32_t flags, void *stream) {
     if (int rc = check_engine(e)) return rc;
     if (n_guesses < 0) return fail(CM_ERR_INVALID, "n_guesses %d is negative", n_guesses);
     if (n_slots < 1 || n_slots > CM_MAX_SEQ)
@@ -500,9 +589,11 @@ int cm_score_batch_device(cm_engine *e, const int32_t *d_guess_idx, const int32_
         return fail(CM_ERR_INVALID, "a required device pointer is NULL");
     if (e->n_answers < 1) return fail(CM_ERR_STATE, "cm_set_answers has not been called");
     DeviceGuard guard(e->device);
-    cudaStream_t st = stream ? (cudaStream_t)stream : e->stream;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (flags & ~(uint32_t)CM_SCORE_OVERLAP_PREVIOUS)
+        return fail(CM_ERR_INVALID, "unknown flag bits 0x%x", flags);
 #define CM_CALL(V) launch_score<V>(e, d_guess_idx, d_guess_len, n_guesses, n_slots, \
-                                   d_answer_slot, d_exact, min_score, d_scores, d_centi, st)
+                                   d_answer_slot, d_exact, min_score, d_scores, d_centi, flags, st)
     CM_DISPATCH_VPL(e->dim, CM_CALL)
 #undef CM_CALL
     CM_CUDA(cudaGetLastError());
@@ -545,7 +636,7 @@ int cm_score_batch_host(cm_engine *e, const int32_t *guess_idx, const int32_t *g
         n_guesses, n_slots, (const int32_t *)(e->d_stage + off_slot),
         exact ? (const uint8_t *)(e->d_stage + off_exact) : nullptr, min_score,
         (float *)(e->d_stage + off_scores), centi ? (int32_t *)(e->d_stage + off_centi) : nullptr,
-        e->stream);
+        0u, e->stream);
     if (rc != CM_OK) return rc;
     CM_CUDA(cudaMemcpyAsync(e->h_stage + off_scores, e->d_stage + off_scores, total - in_bytes,
                             cudaMemcpyDeviceToHost, e->stream));

@@ -84,17 +84,21 @@ class ScoringEngine:
         check(self._lib.cm_engine_synchronize(self._h))
 
     # ---- answers ---------------------------------------------------------------------
-    def set_answers(self, rows: Sequence[int], stream: int = 0) -> None:
+    def _stream(self, stream: Optional[int]) -> int:
+        # None = the engine's own stream; an int (0 included: CUDA's default stream) is used as is
+        return self.stream if stream is None else int(stream)
+
+    def set_answers(self, rows: Sequence[int], stream: Optional[int] = None) -> None:
         """Register the round's hidden words (table rows, -1 = unknown word)."""
         key = tuple(int(r) for r in rows)
         if key == self._answers:
             return
         arr = np.asarray(key, dtype=np.int32)
-        check(self._lib.cm_set_answers(self._h, arr.ctypes.data, arr.size, stream or None))
+        check(self._lib.cm_set_answers(self._h, arr.ctypes.data, arr.size, self._stream(stream) or None))
         self._answers = key
 
-    def set_answers_device(self, d_rows: int, n: int, stream: int = 0) -> None:
-        check(self._lib.cm_set_answers_device(self._h, d_rows, n, stream or None))
+    def set_answers_device(self, d_rows: int, n: int, stream: Optional[int] = None) -> None:
+        check(self._lib.cm_set_answers_device(self._h, d_rows, n, self._stream(stream) or None))
         self._answers = None
 
     @property
@@ -126,9 +130,9 @@ class ScoringEngine:
 
     def score_device(self, d_guess_idx: int, d_guess_len: int, n_guesses: int, n_slots: int,
                      d_answer_slot: int, d_exact: int, min_score: float, d_scores: int,
-                     d_centi: int = 0, stream: int = 0) -> None:
+                     d_centi: int = 0, stream: Optional[int] = None, flags: int = 0) -> None:
         """Asynchronous scoring on buffers already resident in HBM (raw device addresses)."""
         check(self._lib.cm_score_batch_device(
             self._h, d_guess_idx, d_guess_len, n_guesses, n_slots, d_answer_slot,
             d_exact or None, ctypes.c_float(np.float32(min_score)), d_scores, d_centi or None,
-            stream or None))
+            flags, self._stream(stream) or None))

@@ -17,7 +17,9 @@
  *     slots are used; the rest is padding.  N = 1 is the only shape the reference
  *     itself produces; N > 1 is the mean-pool extension (gensim n_similarity).
  *   - answers are registered once per round (cm_set_answers) and referred to by slot.
- *   - `stream` is a cudaStream_t passed as void* (NULL = the engine's own stream).
+ *   - `stream` is a cudaStream_t passed as void*, used as given: NULL is CUDA's default
+ *     stream, exactly as in the runtime API.  cm_engine_stream() returns the engine's own
+ *     non-blocking stream, which the host-buffer entry point uses.
  */
 #ifndef CASSMANTLE_B200_H
 #define CASSMANTLE_B200_H
@@ -41,6 +43,15 @@ typedef enum cm_status {
 #define CM_MAX_DIM 1024        /* vector_size limit; must be a multiple of 4            */
 #define CM_MAX_ANSWERS 4096    /* answer slots per engine                               */
 #define CM_MAX_SEQ 4096        /* word slots per guess                                  */
+
+/* cm_score_batch_device flags.
+ * CM_SCORE_OVERLAP_PREVIOUS: the launch may start gathering table rows while the kernel
+ * launched just before it on the same stream is still finishing (programmatic dependent
+ * launch); it still waits for that kernel before reading the answers or writing results.
+ * Pass it only when the guess buffers of this call (d_guess_idx, d_guess_len,
+ * d_answer_slot, d_exact) were NOT written by that immediately preceding kernel -- e.g. a
+ * stream of independent batches, each filled by a copy or by earlier work.              */
+#define CM_SCORE_OVERLAP_PREVIOUS 0x1u
 
 /* Text of the last error raised on the calling thread ("" if none). */
 const char *cm_last_error(void);
@@ -89,12 +100,14 @@ int cm_set_answers_device(cm_engine *e, const int32_t *d_answer_rows, int n_answ
  *   result = cos if cos > min_score else min_score                    (backend.py:310)
  * d_exact may be NULL (no exact matches).  d_centi may be NULL; when given it receives
  * floor(score * 1e4 + 0.5), the browser's (score*100).toFixed(2) in hundredths
- * (static/script.js:300).  Asynchronous on `stream`; inputs and outputs stay in HBM.     */
+ * (static/script.js:300).  Asynchronous on `stream`; inputs and outputs stay in HBM.
+ * `flags`: 0, or CM_SCORE_OVERLAP_PREVIOUS (see above).                                   */
 int cm_score_batch_device(cm_engine *e,
                           const int32_t *d_guess_idx, const int32_t *d_guess_len,
                           int n_guesses, int n_slots,
                           const int32_t *d_answer_slot, const uint8_t *d_exact,
-                          float min_score, float *d_scores, int32_t *d_centi, void *stream);
+                          float min_score, float *d_scores, int32_t *d_centi,
+                          uint32_t flags, void *stream);
 
 /* Same call with HOST buffers: stages the inputs to the GPU, scores, copies the results
  * back and returns when `scores` (and `centi`, if not NULL) are valid.  This is what the

@@ -143,6 +143,37 @@ def test_device_entry_point_equals_host_entry_point(small_engine):
     assert np.array_equal(out.cpu().numpy().view(np.uint32), want2.view(np.uint32))
 
 
+def test_overlapped_launches_match_serial(small_engine):
+    """CM_SCORE_OVERLAP_PREVIOUS: back-to-back independent batches may overlap on the GPU;
+    every batch must still come out bit-identical to a serial run, including right after
+    the answers change (the kernel waits for its predecessor before it reads them)."""
+    import torch
+    from cassmantle_b200._lib import CM_SCORE_OVERLAP_PREVIOUS
+    dev = torch.device("cuda:0")
+    stream = torch.cuda.Stream(device=dev)
+    B, N, K = 1500, 6, 40
+    batches, want = [], []
+    answers = [np.array([11, 22], np.int32), np.array([333, 4444, 5], np.int32)]
+    for i in range(K):
+        idx, ln, _, slot, ex = synth.make_guess_batch(B, N, 50_000, 2, seed=900 + i, ragged=True)
+        ans = answers[(i // 10) % 2]
+        small_engine.set_answers(ans)
+        want.append(small_engine.score_host(idx, ln, slot, ex, 0.01)[0])
+        batches.append((ans, [torch.from_numpy(a).to(dev) for a in (idx, ln, slot, ex)]))
+    outs = [torch.zeros(B, dtype=torch.float32, device=dev) for _ in range(K)]
+    torch.cuda.synchronize()
+    with torch.cuda.stream(stream):
+        st = stream.cuda_stream
+        for i, (ans, t) in enumerate(batches):
+            small_engine.set_answers(ans, stream=st)          # no-op unless the round changed
+            small_engine.score_device(t[0].data_ptr(), t[1].data_ptr(), B, N, t[2].data_ptr(),
+                                      t[3].data_ptr(), 0.01, outs[i].data_ptr(), 0, stream=st,
+                                      flags=CM_SCORE_OVERLAP_PREVIOUS)
+    torch.cuda.synchronize()
+    for i in range(K):
+        assert np.array_equal(outs[i].cpu().numpy().view(np.uint32), want[i].view(np.uint32)), i
+
+
 # ---------------------------------------------------------------------------------------
 # edge cases the reference's semantics define
 # ---------------------------------------------------------------------------------------
