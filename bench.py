@@ -12,8 +12,9 @@ A step = one pass of the hot path over one batch = one launch of cm_score_kernel
   value  : device-resident inputs, K steps timed with CUDA events on the launch stream,
            max over ranks.  A ring of distinct batches is cycled so consecutive steps touch
            different table rows (uniform over 3.6 GB >> 126 MB of L2).
-  e2e    : the same K steps through the C-ABI host entry point (cm_score_batch_host):
-           pinned host inputs -> H2D -> kernel -> D2H scores, synchronous per call.
+  e2e    : the same K steps through the C-ABI host path (cm_pipe_*): inputs in page-locked
+           host memory -> H2D DMA -> kernel -> scores back in host memory, 4 batches in flight;
+           the blocking one-call-per-step figure (cm_score_batch_host) is reported beside it.
   roofline : the scoring kernel alone, >= 1 s of back-to-back launches timed with CUDA events;
            achieved = algorithmic bytes (N*1204 + 8 per guess) / time.
   cpu_baseline : the oracle's faithful per-pair port of src/backend.py:303-317 (what the
@@ -45,6 +46,7 @@ N_ANSWERS = 2
 MIN_SCORE = 0.01
 RING = 64                      # distinct batches cycled through (64 x 79 MB of rows)
 OVERLAP = 1                    # CM_SCORE_OVERLAP_PREVIOUS: the ring's batches are independent
+PIPE_DEPTH = 4                 # batches in flight on the pipelined host path
 BYTES_PER_GUESS = N * (D * 4 + 4) + 8      # N rows + N indices + len/slot + score
 METRIC = "guesses_scored_per_sec"
 UNIT = "guesses/s"
@@ -213,15 +215,18 @@ def run_own(args) -> None:
         workers = args.cpu_workers or os.cpu_count() or 1
         cpu = CpuScorer(ans, ring, workers)
         rate = calibrate(cpu)
-        n_batches = int(max(1, min(RING, round(rate * args.cpu_budget_s / B))))
+        # bounded sample: about args.cpu_budget_s CPU-seconds summed over the workers
+        wall_budget = max(2.0, args.cpu_budget_s / workers)
+        n_batches = int(max(1, min(8 * RING, round(rate * wall_budget / B))))
         t0 = time.perf_counter()
-        outs = [cpu.score(i, B) for i in range(n_batches)]
+        outs = [cpu.score(i % RING, B) for i in range(n_batches)]
         dt = time.perf_counter() - t0
         single = None
-        if workers > 1:                      # also the literal single-process figure
+        if workers > 1:                      # also the literal one-process figure (the reference
+            _cpu_worker((1, 0, 256))         # runs its scorer on a single event loop)
             t1 = time.perf_counter()
-            _cpu_worker((0, 0, 512))
-            single = 512 / (time.perf_counter() - t1)
+            _cpu_worker((2, 0, 2048))
+            single = 2048 / (time.perf_counter() - t1)
         cpu.close()
         cpu_check = outs
         cpu_baseline = {
@@ -337,23 +342,70 @@ def run_own(args) -> None:
     achieved = B * BYTES_PER_GUESS / (kern_us * 1e-6) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": TRAFFIC_BYTES_PER_LAUNCH,
-                "kernel": "cm_score_kernel<3>", "kernel_us": kern_us, "launches_timed": n_roof,
+                "kernel": "cm_score_kernel<VPL=3,LPG=32,R=2> (4096x16 launches, CM_SCORE_OVERLAP_PREVIOUS)", "kernel_us": kern_us, "launches_timed": n_roof,
                 "algorithmic_bytes_per_launch": B * BYTES_PER_GUESS, "peak_source": peak_src}
 
     # ---- e2e: host buffers through the C ABI ---------------------------------------------
-    for i in range(args.warmup):
-        step_host(i)
+    # (a) pipelined: cm_pipe_* with PIPE_DEPTH batches in flight.  The ring's batches live in
+    #     page-locked host memory (the pipe's slots, filled before the timed region); every
+    #     step DMAs that step's inputs to the GPU, scores them, and the step's scores land
+    #     back in page-locked host memory, where the host reads them.
+    # (b) synchronous: one cm_score_batch_host call per step (what Backend.compute_scores uses).
+    from cassmantle_b200.engine import ScoringPipe
+    pipe = ScoringPipe(eng, depth=RING, max_guesses=B, max_slots=N)
+    views = []
+    for s_i, (idx, ln, slot, ex) in enumerate(ring):
+        v = pipe.buffers(s_i, B, N)
+        v["guess_idx"][:] = idx
+        v["guess_len"][:] = ln
+        v["answer_slot"][:] = slot
+        v["exact"][:] = ex
+        views.append(v)
+    submit, wait, ph = lib.cm_pipe_submit, lib.cm_pipe_wait, pipe._h
+    checksum = 0.0
+
+    def run_pipe(first: int, count: int) -> None:
+        nonlocal checksum
+        for i in range(first, first + count):
+            if i - first >= PIPE_DEPTH:
+                j = (i - PIPE_DEPTH) % RING
+                wait(ph, j)
+                checksum += float(views[j]["scores"][0])       # the host consumes the result
+            if submit(ph, i % RING, ms32, 0) != 0:
+                _lib.check(-1)
+        for i in range(max(first, first + count - PIPE_DEPTH), first + count):
+            j = i % RING
+            wait(ph, j)
+            checksum += float(views[j]["scores"][0])
+
+    run_pipe(0, max(args.warmup, PIPE_DEPTH))
     barrier()
+    launches1 = lib.cm_kernel_launch_count()
     t0 = time.perf_counter()
-    for i in range(args.steps):
-        step_host(args.warmup + i)
-    torch.cuda.synchronize()
+    run_pipe(args.warmup, args.steps)
     e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e_launches = int(lib.cm_kernel_launch_count() - launches1)
     h2d = B * N * 4 + B * 4 + B * 4 + B
     e2e = {"value": args.steps * B * world / e2e_s, "unit": UNIT,
            "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 4,
-           "ms_per_step": e2e_s / args.steps * 1e3,
-           "api": "cm_score_batch_host (C ABI, pinned host buffers, synchronous per call)"}
+           "ms_per_step": e2e_s / args.steps * 1e3, "gpu_launches": e2e_launches,
+           "api": f"cm_pipe_submit/cm_pipe_wait (C ABI), {PIPE_DEPTH} batches in flight, inputs DMA'd "
+                  f"from page-locked host slots, scores written back into them by the kernel"}
+    for i in range(args.warmup):
+        step_host(i)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    n_sync = min(args.steps, 2000)
+    for i in range(n_sync):
+        step_host(args.warmup + i)
+    sync_s = time.perf_counter() - t0
+    e2e["synchronous_call"] = {"value": n_sync * B / sync_s, "unit": UNIT, "ms_per_step": sync_s / n_sync * 1e3,
+                               "api": "cm_score_batch_host, one blocking call per step, pinned buffers"}
+    # parity of the pipelined path against the synchronous one on a few slots
+    for j in range(3):
+        step_host(j)
+        assert np.array_equal(h_scores_np.view(np.uint32),
+                              np.asarray(views[j]["scores"]).view(np.uint32)) or args.steps < RING
 
     # ---- single-call latency on the micro-batch shape (configs[1]: 512 guesses x 8) ------
     lat = None
@@ -401,8 +453,8 @@ def run_own(args) -> None:
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of cm_score_kernel at 4096x16 from the
-# committed `ncu --set full` capture (profiles/); None until a capture exists.
-TRAFFIC_BYTES_PER_LAUNCH = None
+# committed `ncu --set full` capture (profiles/).
+TRAFFIC_BYTES_PER_LAUNCH = 81_421_568   # profiles/r1_v2_4096x16.summary.txt (79.75 MB read + 1.67 MB written)
 
 
 def main() -> None:
@@ -412,7 +464,7 @@ def main() -> None:
     ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
     ap.add_argument("--cpu-workers", type=int, default=0, help="0 = all cores")
-    ap.add_argument("--cpu-budget-s", type=float, default=12.0)
+    ap.add_argument("--cpu-budget-s", type=float, default=20.0, help="CPU-seconds of baseline work")
     ap.add_argument("--ref-budget-s", type=float, default=60.0)
     ap.add_argument("--roofline-s", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")

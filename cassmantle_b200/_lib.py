@@ -48,6 +48,12 @@ _SIGNATURES = {
     "cm_set_answers_device": (_c.c_int, [_P, _P, _c.c_int, _P]),
     "cm_score_batch_device": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _P, _P, _c.c_float,
                                          _P, _P, _c.c_uint32, _P]),
+    "cm_pipe_create": (_c.c_int, [_c.POINTER(_P), _P, _c.c_int, _c.c_int, _c.c_int]),
+    "cm_pipe_destroy": (_c.c_int, [_P]),
+    "cm_pipe_depth": (_c.c_int, [_P]),
+    "cm_pipe_buffers": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_int] + [_c.POINTER(_P)] * 6),
+    "cm_pipe_submit": (_c.c_int, [_P, _c.c_int, _c.c_float, _c.c_int]),
+    "cm_pipe_wait": (_c.c_int, [_P, _c.c_int]),
     "cm_score_batch_host": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _P, _P, _c.c_float,
                                        _P, _P]),
 }

@@ -1,0 +1,165 @@
+// cassmantle_b200 -- pipelined host path (include/cassmantle_b200.h: cm_pipe_*).
+//
+// A pipe is a ring of `depth` slots.  Each slot owns a page-locked host block that the caller
+// fills in place (no staging copy), a device block the inputs are DMA'd into, a stream and an
+// event.  cm_pipe_submit() enqueues  H2D copy -> scoring kernel  on the slot's stream; the
+// kernel writes the scores straight back into the slot's page-locked block, so there is no
+// D2H copy to schedule.  With two or more slots the copy of batch i+1 runs on the copy engine
+// while batch i is being scored, and the host fills batch i+2.
+//
+// This is the device-side half of the request micro-batcher that north_star places in
+// src/server.py (cassmantle_b200/server.py drives it); the reference has no counterpart.
+
+#include <cuda_runtime.h>
+
+#include <new>
+#include <vector>
+
+#include "cm_internal.h"
+
+struct cm_pipe_slot {
+    unsigned char *h = nullptr;     // pinned: [idx | len | slot | exact | scores | centi]
+    unsigned char *d = nullptr;     // device: [idx | len | slot | exact]
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    int n_guesses = 0, n_slots = 0;
+    size_t off_len = 0, off_slot = 0, off_exact = 0, in_bytes = 0, off_scores = 0, off_centi = 0;
+    bool in_flight = false;
+};
+
+struct cm_pipe {
+    cm_engine *engine = nullptr;
+    int max_guesses = 0, max_slots = 0;
+    size_t slot_bytes = 0;
+    std::vector<cm_pipe_slot> slots;
+};
+
+namespace {
+
+using cm::align_up;
+using cm::fail;
+
+void layout(cm_pipe_slot &s, size_t B, size_t N) {
+    s.off_len = align_up(B * N * 4, 16);
+    s.off_slot = s.off_len + align_up(B * 4, 16);
+    s.off_exact = s.off_slot + align_up(B * 4, 16);
+    s.in_bytes = align_up(s.off_exact + B, 256);
+    s.off_scores = s.in_bytes;
+    s.off_centi = s.off_scores + align_up(B * 4, 16);
+}
+
+int check_slot(const cm_pipe *p, int slot) {
+    if (p == nullptr) return fail(CM_ERR_INVALID, "pipe is NULL");
+    if (slot < 0 || slot >= (int)p->slots.size())
+        return fail(CM_ERR_INVALID, "slot %d not in [0, %d)", slot, (int)p->slots.size());
+    return CM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int cm_pipe_destroy(cm_pipe *p) {
+    if (p == nullptr) return CM_OK;
+    {
+        cm::DeviceGuard guard(p->engine->device);
+        for (auto &s : p->slots) {
+            if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); }
+            if (s.done) cudaEventDestroy(s.done);
+            if (s.d) cudaFree(s.d);
+            if (s.h) cudaFreeHost(s.h);
+        }
+    }
+    delete p;
+    return CM_OK;
+}
+
+int cm_pipe_create(cm_pipe **out, cm_engine *e, int depth, int max_guesses, int max_slots) {
+    if (out == nullptr) return fail(CM_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    if (int rc = cm::check_engine(e)) return rc;
+    if (depth < 1 || depth > 64) return fail(CM_ERR_INVALID, "depth %d outside [1, 64]", depth);
+    if (max_guesses < 1) return fail(CM_ERR_INVALID, "max_guesses %d < 1", max_guesses);
+    if (max_slots < 1 || max_slots > CM_MAX_SEQ)
+        return fail(CM_ERR_INVALID, "max_slots %d outside [1, %d]", max_slots, CM_MAX_SEQ);
+    cm_pipe *p = new (std::nothrow) cm_pipe();
+    if (p == nullptr) return fail(CM_ERR_NOMEM, "pipe allocation failed");
+    p->engine = e;
+    p->max_guesses = max_guesses;
+    p->max_slots = max_slots;
+    cm_pipe_slot probe;
+    layout(probe, (size_t)max_guesses, (size_t)max_slots);
+    p->slot_bytes = probe.off_centi + align_up((size_t)max_guesses * 4, 256);
+    p->slots.resize(depth);
+    cm::DeviceGuard guard(e->device);
+    for (auto &s : p->slots) {
+        cudaError_t err = cudaHostAlloc(&s.h, p->slot_bytes, cudaHostAllocDefault);
+        if (err == cudaSuccess) err = cudaMalloc(&s.d, probe.in_bytes);
+        if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
+        if (err == cudaSuccess) err = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming);
+        if (err != cudaSuccess) {
+            cudaGetLastError();
+            const int code = fail(err == cudaErrorMemoryAllocation ? CM_ERR_NOMEM : CM_ERR_CUDA,
+                                  "pipe slot setup (%zu bytes) failed: %s", p->slot_bytes,
+                                  cudaGetErrorString(err));
+            cm_pipe_destroy(p);
+            return code;
+        }
+    }
+    *out = p;
+    return CM_OK;
+}
+
+int cm_pipe_buffers(cm_pipe *p, int slot, int n_guesses, int n_slots, int32_t **guess_idx,
+                    int32_t **guess_len, int32_t **answer_slot, uint8_t **exact, float **scores,
+                    int32_t **centi) {
+    if (int rc = check_slot(p, slot)) return rc;
+    if (n_guesses < 1 || n_guesses > p->max_guesses)
+        return fail(CM_ERR_INVALID, "n_guesses %d outside [1, %d]", n_guesses, p->max_guesses);
+    if (n_slots < 1 || n_slots > p->max_slots)
+        return fail(CM_ERR_INVALID, "n_slots %d outside [1, %d]", n_slots, p->max_slots);
+    cm_pipe_slot &s = p->slots[slot];
+    if (s.in_flight) return fail(CM_ERR_STATE, "slot %d is in flight; cm_pipe_wait it first", slot);
+    s.n_guesses = n_guesses;
+    s.n_slots = n_slots;
+    layout(s, (size_t)n_guesses, (size_t)n_slots);
+    if (guess_idx) *guess_idx = (int32_t *)s.h;
+    if (guess_len) *guess_len = (int32_t *)(s.h + s.off_len);
+    if (answer_slot) *answer_slot = (int32_t *)(s.h + s.off_slot);
+    if (exact) *exact = s.h + s.off_exact;
+    if (scores) *scores = (float *)(s.h + s.off_scores);
+    if (centi) *centi = (int32_t *)(s.h + s.off_centi);
+    return CM_OK;
+}
+
+int cm_pipe_submit(cm_pipe *p, int slot, float min_score, int want_centi) {
+    if (int rc = check_slot(p, slot)) return rc;
+    cm_pipe_slot &s = p->slots[slot];
+    if (s.n_guesses < 1) return fail(CM_ERR_STATE, "slot %d has no batch; call cm_pipe_buffers", slot);
+    if (s.in_flight) return fail(CM_ERR_STATE, "slot %d is already in flight", slot);
+    cm_engine *e = p->engine;
+    cm::DeviceGuard guard(e->device);
+    CM_CUDA(cudaMemcpyAsync(s.d, s.h, s.in_bytes, cudaMemcpyHostToDevice, s.stream));
+    if (int rc = cm::enqueue_score(e, (const int32_t *)s.d, (const int32_t *)(s.d + s.off_len),
+                                   s.n_guesses, s.n_slots, (const int32_t *)(s.d + s.off_slot),
+                                   s.d + s.off_exact, min_score, (float *)(s.h + s.off_scores),
+                                   want_centi ? (int32_t *)(s.h + s.off_centi) : nullptr, 0u, s.stream))
+        return rc;
+    CM_CUDA(cudaEventRecord(s.done, s.stream));
+    s.in_flight = true;
+    return CM_OK;
+}
+
+int cm_pipe_wait(cm_pipe *p, int slot) {
+    if (int rc = check_slot(p, slot)) return rc;
+    cm_pipe_slot &s = p->slots[slot];
+    if (!s.in_flight) return CM_OK;
+    cm::DeviceGuard guard(p->engine->device);
+    CM_CUDA(cudaEventSynchronize(s.done));
+    s.in_flight = false;
+    return CM_OK;
+}
+
+int cm_pipe_depth(cm_pipe *p) { return p ? (int)p->slots.size() : 0; }
+
+}  // extern "C"

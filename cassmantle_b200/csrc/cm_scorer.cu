@@ -19,13 +19,13 @@
 #include <mutex>
 #include <new>
 
-#include "../../include/cassmantle_b200.h"
 #include "cm_common.cuh"
+#include "cm_internal.h"
 
-namespace {
+namespace cm {
 
-thread_local char g_err[512] = "";
-std::atomic<int64_t> g_launches{0};
+static thread_local char g_err[512] = "";
+static std::atomic<int64_t> g_launches{0};
 
 int fail(int code, const char *fmt, ...) {
     va_list ap;
@@ -35,25 +35,14 @@ int fail(int code, const char *fmt, ...) {
     return code;
 }
 
-#define CM_CUDA(expr)                                                                   \
-    do {                                                                                \
-        cudaError_t err__ = (expr);                                                     \
-        if (err__ != cudaSuccess)                                                       \
-            return fail(CM_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(err__)); \
-    } while (0)
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
-struct DeviceGuard {
-    int prev = -1;
-    bool ok = true;
-    explicit DeviceGuard(int dev) {
-        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
-        if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
-    }
-    ~DeviceGuard() {
-        int cur = -1;
-        if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
-    }
-};
+}  // namespace cm
+
+namespace {
+
+using cm::DeviceGuard;
+using cm::fail;
 
 constexpr int kWarpsPerCta = 8;
 
@@ -112,13 +101,30 @@ __device__ __forceinline__ void group_unitvec(float4 (&m)[VPL]) {
     }
     ss = group_sum<LPG>(ss);
     if (ss > 0.0) {
+        // (float)((double)x * inv) without going through the conversion pipe for every element:
+        // inv = ih + il to ~2^-48, so fma(x, ih, x*il) rounds the same exact product once.
         const double inv = 1.0 / sqrt(ss);
+        const float ih = (float)inv;
+        if (ih > 1e-30f && ih < 1e30f) {
+            const float il = (float)(inv - (double)ih);
 #pragma unroll
-        for (int v = 0; v < VPL; ++v) {
-            m[v].x = (float)((double)m[v].x * inv);
-            m[v].y = (float)((double)m[v].y * inv);
-            m[v].z = (float)((double)m[v].z * inv);
-            m[v].w = (float)((double)m[v].w * inv);
+            for (int v = 0; v < VPL; ++v) {
+                m[v].x = fmaf(m[v].x, ih, __fmul_rn(m[v].x, il));
+                m[v].y = fmaf(m[v].y, ih, __fmul_rn(m[v].y, il));
+                m[v].z = fmaf(m[v].z, ih, __fmul_rn(m[v].z, il));
+                m[v].w = fmaf(m[v].w, ih, __fmul_rn(m[v].w, il));
+            }
+        } else {                                   // norms near the ends of the fp32 range
+#pragma unroll
+            for (int v = 0; v < VPL; ++v) {
+                float4 t = m[v];
+                // launder: keeps the compiler from holding 4*VPL doubles live for this cold path
+                asm volatile("" : "+f"(t.x), "+f"(t.y), "+f"(t.z), "+f"(t.w));
+                m[v].x = (float)((double)t.x * inv);
+                m[v].y = (float)((double)t.y * inv);
+                m[v].z = (float)((double)t.z * inv);
+                m[v].w = (float)((double)t.w * inv);
+            }
         }
     }
 }
@@ -161,7 +167,7 @@ cm_answer_unit_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
 //   phase 2  / N, unitvec through an fp64 norm, fp32 dot with the answer's unit vector,
 //            floor at min_score, optional hundredths of a percent
 // --------------------------------------------------------------------------------------
-template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS>
+template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
                 const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
@@ -191,18 +197,24 @@ cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
     const bool is_exact = (exact != nullptr) && (exact[b] != 0);
     int n = guess_len[b];
     const int slot = answer_slot[b];
-    int32_t mine = (sub < n_slots) ? gi[sub] : -1;
+    // SINGLE (n_slots == 1, the reference's own shape): every lane of the group reads the one index
+    int32_t mine = SINGLE ? gi[0] : ((sub < n_slots) ? gi[sub] : -1);
     n = n < 0 ? 0 : (n > n_slots ? n_slots : n);
     const bool slot_ok = slot >= 0 && slot < n_answers;
 
     // KeyError scan: a used slot outside the table, an empty guess, or an unknown answer.
-    bool bad = (sub < n) && (mine < 0 || (int64_t)mine >= n_rows);
-    for (int c = LPG + sub; c < n; c += LPG) {
-        const int32_t r = gi[c];
-        bad |= (r < 0) || ((int64_t)r >= n_rows);
+    bool bad;
+    if constexpr (SINGLE) {
+        bad = (n > 0) && (mine < 0 || (int64_t)mine >= n_rows);
+    } else {
+        bad = (sub < n) && (mine < 0 || (int64_t)mine >= n_rows);
+        for (int c = LPG + sub; c < n; c += LPG) {
+            const int32_t r = gi[c];
+            bad |= (r < 0) || ((int64_t)r >= n_rows);
+        }
+        const unsigned gmask = (LPG == 32) ? cm::kFullMask : (((1u << LPG) - 1u) << grp_base);
+        bad = (__ballot_sync(cm::kFullMask, bad) & gmask) != 0u;
     }
-    const unsigned gmask = (LPG == 32) ? cm::kFullMask : (((1u << LPG) - 1u) << grp_base);
-    bad = (__ballot_sync(cm::kFullMask, bad) & gmask) != 0u;
     bad = bad || n == 0 || !slot_ok;
     const bool active = have && !is_exact && !bad;
     const int n_live = active ? n : 0;
@@ -214,6 +226,14 @@ cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
     const float4 *table4 = reinterpret_cast<const float4 *>(table);
 
     // ---- phase 1: gather ------------------------------------------------------------------
+    if constexpr (SINGLE) {                                  // one row, straight into acc
+        const float4 *src = table4 + (size_t)(n_live > 0 ? mine : 0) * dim4;
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+            const int j = sub + LPG * v;
+            if (n_live > 0 && j < dim4) acc[v] = STREAM ? cm::ld_stream_f4(src + j) : __ldg(src + j);
+        }
+    } else
     for (int c = 0; c < n_max; c += LPG) {
         if (c > 0) mine = (c + sub < n_live) ? gi[c + sub] : 0;
         const int m = min(LPG, n_max - c);
@@ -252,7 +272,7 @@ cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
         const int32_t ar = slot_ok ? ans_rows[slot] : -1;     // unknown answer = KeyError too
         bad = bad || ar < 0 || (int64_t)ar >= n_rows;
     }
-    if (n_max > 1) {                                         // warp-uniform; x / 1 is exact anyway
+    if (!SINGLE && n_max > 1) {                              // warp-uniform; x / 1 is exact anyway
         const float fn = (float)(n_live > 1 ? n_live : 1);
 #pragma unroll
         for (int v = 0; v < VPL; ++v) {
@@ -291,28 +311,12 @@ cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
 
 }  // namespace
 
-struct cm_engine {
-    int device = 0;
-    int64_t n_rows = 0;
-    int dim = 0;
-    float *d_table = nullptr;
-    float *d_ans_unit = nullptr;     // [CM_MAX_ANSWERS][dim] unit vectors of the round's answers
-    int32_t *d_ans_rows = nullptr;   // [CM_MAX_ANSWERS] their table rows (-1 = not in vocabulary)
-    int n_answers = 0;
-    cudaStream_t stream = nullptr;
-    // staging for the host-buffer entry point (grown on demand, reused across calls)
-    unsigned char *d_stage = nullptr;
-    unsigned char *h_stage = nullptr;
-    size_t stage_bytes = 0;
-    std::mutex mu;
-};
-
 namespace {
 
 // Kernel variants.  `CM_SCORE_VARIANT` (environment, read once) forces one for tuning runs.
 //   wide   : 32 lanes per guess, R rows per round   -- phrases (N >= 3) and any table width
 //   narrow : 8 lanes per guess, 4 guesses per warp   -- one- and two-word guesses, dim 300 only
-template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS>
+template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE = false>
 void launch_variant(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
                     const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
                     int32_t *centi, uint32_t flags, cudaStream_t st) {
@@ -326,11 +330,11 @@ void launch_variant(const cm_engine *e, const int32_t *gi, const int32_t *gl, in
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaLaunchKernelEx(&cfg, cm_score_kernel<VPL, LPG, R, STREAM, THREADS, MIN_BLOCKS>,
+    cudaLaunchKernelEx(&cfg, cm_score_kernel<VPL, LPG, R, STREAM, THREADS, MIN_BLOCKS, SINGLE>,
                        (const float *)e->d_table, e->n_rows, e->dim / 4, gi, gl, B, N,
                        (const float *)e->d_ans_unit, (const int32_t *)e->d_ans_rows, e->n_answers,
                        slot, exact, min_score, scores, centi, flags);
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+    cm::count_launch();
 }
 
 int forced_variant() {
@@ -347,11 +351,20 @@ void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int 
                   int32_t *centi, uint32_t flags, cudaStream_t st) {
 #define CM_V(LPG, R, STREAM, THREADS, MINB, VP) \
     launch_variant<VP, LPG, R, STREAM, THREADS, MINB>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st)
+#define CM_S(LPG, STREAM, THREADS, MINB, VP) \
+    launch_variant<VP, LPG, 1, STREAM, THREADS, MINB, true>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st)
     if constexpr (VPL == 3) {
         if (e->dim == 300) {
             int variant = forced_variant();
-            if (variant == 0) variant = (N <= 2) ? 7 : 8;
+            if (variant == 0) variant = (N == 1) ? 20 : 8;
+            if (variant >= 20 && N != 1) variant = 8;
             switch (variant) {
+                case 20: CM_S(8, true, 128, 8, 10); return;
+                case 21: CM_S(8, true, 128, 6, 10); return;
+                case 22: CM_S(8, false, 128, 8, 10); return;
+                case 23: CM_S(16, true, 128, 8, 5); return;
+                case 24: CM_S(32, true, 128, 8, 3); return;
+                case 25: CM_S(8, true, 256, 4, 10); return;
                 case 1: CM_V(32, 4, true, 128, 7, 3); return;
                 case 2: CM_V(32, 8, true, 128, 4, 3); return;
                 case 3: CM_V(8, 1, false, 128, 5, 10); return;
@@ -372,6 +385,7 @@ void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int 
     }
     CM_V(32, 4, true, 256, 1, VPL);
 #undef CM_V
+#undef CM_S
 }
 
 template <int VPL>
@@ -379,7 +393,7 @@ void launch_answers(const cm_engine *e, const int32_t *d_rows, int A, cudaStream
     const int grid = (A + kWarpsPerCta - 1) / kWarpsPerCta;
     cm_answer_unit_kernel<VPL><<<grid, kWarpsPerCta * 32, 0, st>>>(
         e->d_table, e->n_rows, e->dim / 4, d_rows, A, e->d_ans_unit);
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+    cm::count_launch();
 }
 
 #define CM_DISPATCH_VPL(dim, CALL)                          \
@@ -394,44 +408,79 @@ void launch_answers(const cm_engine *e, const int32_t *d_rows, int A, cudaStream
         default: CALL(8); break;                            \
     }
 
+}  // namespace
+
+namespace cm {
+
 int check_engine(const cm_engine *e) {
     if (e == nullptr) return fail(CM_ERR_INVALID, "engine is NULL");
     if (e->d_table == nullptr) return fail(CM_ERR_STATE, "engine has no resident table");
     return CM_OK;
 }
 
-int ensure_stage(cm_engine *e, size_t bytes) {
+bool is_pinned_host(const void *p) {
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return attr.type == cudaMemoryTypeHost;
+}
+
+int enqueue_score(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_len, int n_guesses,
+                  int n_slots, const int32_t *answer_slot, const uint8_t *exact, float min_score,
+                  float *scores, int32_t *centi, uint32_t flags, cudaStream_t st) {
+    if (int rc = check_engine(e)) return rc;
+    if (n_guesses < 0) return fail(CM_ERR_INVALID, "n_guesses %d is negative", n_guesses);
+    if (n_slots < 1 || n_slots > CM_MAX_SEQ)
+        return fail(CM_ERR_INVALID, "n_slots %d outside [1, %d]", n_slots, CM_MAX_SEQ);
+    if (flags & ~(uint32_t)CM_SCORE_OVERLAP_PREVIOUS)
+        return fail(CM_ERR_INVALID, "unknown flag bits 0x%x", flags);
+    if (n_guesses == 0) return CM_OK;
+    if (!guess_idx || !guess_len || !answer_slot || !scores)
+        return fail(CM_ERR_INVALID, "a required buffer pointer is NULL");
+    if (e->n_answers < 1) return fail(CM_ERR_STATE, "cm_set_answers has not been called");
+    DeviceGuard guard(e->device);
+#define CM_CALL(V) launch_score<V>(e, guess_idx, guess_len, n_guesses, n_slots, answer_slot, exact, \
+                                   min_score, scores, centi, flags, st)
+    CM_DISPATCH_VPL(e->dim, CM_CALL)
+#undef CM_CALL
+    CM_CUDA(cudaGetLastError());
+    return CM_OK;
+}
+
+// Pinned staging block of the host entry point (only used when the caller's memory is pageable).
+static int ensure_stage(cm_engine *e, size_t bytes) {
     if (bytes <= e->stage_bytes) return CM_OK;
     size_t want = e->stage_bytes ? e->stage_bytes : (size_t)1 << 20;
     while (want < bytes) want *= 2;
-    if (e->d_stage) cudaFree(e->d_stage);
     if (e->h_stage) cudaFreeHost(e->h_stage);
-    e->d_stage = nullptr; e->h_stage = nullptr; e->stage_bytes = 0;
-    if (cudaMalloc(&e->d_stage, want) != cudaSuccess) {
-        cudaGetLastError();
-        return fail(CM_ERR_NOMEM, "cudaMalloc of %zu staging bytes failed", want);
-    }
+    e->h_stage = nullptr;
+    e->stage_bytes = 0;
     if (cudaHostAlloc(&e->h_stage, want, cudaHostAllocDefault) != cudaSuccess) {
         cudaGetLastError();
-        cudaFree(e->d_stage); e->d_stage = nullptr;
         return fail(CM_ERR_NOMEM, "cudaHostAlloc of %zu staging bytes failed", want);
     }
     e->stage_bytes = want;
     return CM_OK;
 }
 
-inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+}  // namespace cm
 
-}  // namespace
+using cm::align_up;
+using cm::check_engine;
+using cm::DeviceGuard;
+using cm::fail;
+using cm::is_pinned_host;
 
 // ======================================================================================
 // C ABI
 // ======================================================================================
 extern "C" {
 
-const char *cm_last_error(void) { return g_err; }
+const char *cm_last_error(void) { return cm::g_err; }
 const char *cm_version(void) { return "0.1.0"; }
-int64_t cm_kernel_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+int64_t cm_kernel_launch_count(void) { return cm::g_launches.load(std::memory_order_relaxed); }
 
 int cm_engine_create(cm_engine **out, int device, int64_t n_rows, int dim) {
     if (out == nullptr) return fail(CM_ERR_INVALID, "out is NULL");
@@ -479,7 +528,6 @@ int cm_engine_destroy(cm_engine *e) {
         if (e->d_table) cudaFree(e->d_table);
         if (e->d_ans_unit) cudaFree(e->d_ans_unit);
         if (e->d_ans_rows) cudaFree(e->d_ans_rows);
-        if (e->d_stage) cudaFree(e->d_stage);
         if (e->h_stage) cudaFreeHost(e->h_stage);
     }
     delete e;
@@ -518,7 +566,7 @@ int cm_engine_fill_synthetic(cm_engine *e, uint32_t seed) {
         return fail(CM_ERR_INVALID, "synthetic fill needs n_rows*dim < 2^32");
     DeviceGuard guard(e->device);
     cm_synth_fill_kernel<<<148 * 8, 256, 0, e->stream>>>(e->d_table, e->n_rows, e->dim, seed);
-    g_launches.fetch_add(1, std::memory_order_relaxed);
+    cm::count_launch();
     CM_CUDA(cudaGetLastError());
     CM_CUDA(cudaStreamSynchronize(e->stream));
     return CM_OK;
@@ -580,24 +628,8 @@ int cm_score_batch_device(cm_engine *e, const int32_t *d_guess_idx, const int32_
                           int n_guesses, int n_slots, const int32_t *d_answer_slot,
                           const uint8_t *d_exact, float min_score, float *d_scores,
                           int32_t *d_centi, uint32_t flags, void *stream) {
-    if (int rc = check_engine(e)) return rc;
-    if (n_guesses < 0) return fail(CM_ERR_INVALID, "n_guesses %d is negative", n_guesses);
-    if (n_slots < 1 || n_slots > CM_MAX_SEQ)
-        return fail(CM_ERR_INVALID, "n_slots %d outside [1, %d]", n_slots, CM_MAX_SEQ);
-    if (n_guesses == 0) return CM_OK;
-    if (!d_guess_idx || !d_guess_len || !d_answer_slot || !d_scores)
-        return fail(CM_ERR_INVALID, "a required device pointer is NULL");
-    if (e->n_answers < 1) return fail(CM_ERR_STATE, "cm_set_answers has not been called");
-    DeviceGuard guard(e->device);
-    cudaStream_t st = (cudaStream_t)stream;
-    if (flags & ~(uint32_t)CM_SCORE_OVERLAP_PREVIOUS)
-        return fail(CM_ERR_INVALID, "unknown flag bits 0x%x", flags);
-#define CM_CALL(V) launch_score<V>(e, d_guess_idx, d_guess_len, n_guesses, n_slots, \
-                                   d_answer_slot, d_exact, min_score, d_scores, d_centi, flags, st)
-    CM_DISPATCH_VPL(e->dim, CM_CALL)
-#undef CM_CALL
-    CM_CUDA(cudaGetLastError());
-    return CM_OK;
+    return cm::enqueue_score(e, d_guess_idx, d_guess_len, n_guesses, n_slots, d_answer_slot, d_exact,
+                             min_score, d_scores, d_centi, flags, (cudaStream_t)stream);
 }
 
 int cm_score_batch_host(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_len,
@@ -612,37 +644,49 @@ int cm_score_batch_host(cm_engine *e, const int32_t *guess_idx, const int32_t *g
         return fail(CM_ERR_INVALID, "a required host pointer is NULL");
     if (e->n_answers < 1) return fail(CM_ERR_STATE, "cm_set_answers has not been called");
 
-    std::lock_guard<std::mutex> lock(e->mu);     // one staging area: callers take turns
+    // One synchronous call = one kernel launch and no DMA: the kernel reads the batch from
+    // page-locked host memory and writes the scores back into it across PCIe.  Pageable
+    // buffers are first copied into the engine's own pinned block.
+    std::lock_guard<std::mutex> lock(e->mu);     // one staging block: callers take turns
     DeviceGuard guard(e->device);
     const size_t B = (size_t)n_guesses, N = (size_t)n_slots;
-    // one packed block each way: [idx | len | slot | exact] in, [scores | centi] out
-    const size_t off_idx = 0;
-    const size_t off_len = off_idx + B * N * 4;
+    const bool in_pinned = is_pinned_host(guess_idx) && is_pinned_host(guess_len) &&
+                           is_pinned_host(answer_slot) && (!exact || is_pinned_host(exact));
+    const bool out_pinned = is_pinned_host(scores) && (!centi || is_pinned_host(centi));
+    const size_t off_len = align_up(B * N * 4, 16);
     const size_t off_slot = off_len + B * 4;
     const size_t off_exact = off_slot + B * 4;
-    const size_t in_bytes = align_up(off_exact + (exact ? B : 0), 256);
-    const size_t off_scores = in_bytes;
+    const size_t off_scores = align_up(off_exact + B, 16);
     const size_t off_centi = off_scores + B * 4;
-    const size_t total = align_up(off_centi + (centi ? B * 4 : 0), 256);
-    if (int rc = ensure_stage(e, total)) return rc;
+    if (!in_pinned || !out_pinned)
+        if (int rc = cm::ensure_stage(e, off_centi + B * 4)) return rc;
 
-    memcpy(e->h_stage + off_idx, guess_idx, B * N * 4);
-    memcpy(e->h_stage + off_len, guess_len, B * 4);
-    memcpy(e->h_stage + off_slot, answer_slot, B * 4);
-    if (exact) memcpy(e->h_stage + off_exact, exact, B);
-    CM_CUDA(cudaMemcpyAsync(e->d_stage, e->h_stage, in_bytes, cudaMemcpyHostToDevice, e->stream));
-    int rc = cm_score_batch_device(
-        e, (const int32_t *)(e->d_stage + off_idx), (const int32_t *)(e->d_stage + off_len),
-        n_guesses, n_slots, (const int32_t *)(e->d_stage + off_slot),
-        exact ? (const uint8_t *)(e->d_stage + off_exact) : nullptr, min_score,
-        (float *)(e->d_stage + off_scores), centi ? (int32_t *)(e->d_stage + off_centi) : nullptr,
-        0u, e->stream);
-    if (rc != CM_OK) return rc;
-    CM_CUDA(cudaMemcpyAsync(e->h_stage + off_scores, e->d_stage + off_scores, total - in_bytes,
-                            cudaMemcpyDeviceToHost, e->stream));
+    const int32_t *k_idx = guess_idx, *k_len = guess_len, *k_slot = answer_slot;
+    const uint8_t *k_exact = exact;
+    float *k_scores = scores;
+    int32_t *k_centi = centi;
+    if (!in_pinned) {
+        memcpy(e->h_stage, guess_idx, B * N * 4);
+        memcpy(e->h_stage + off_len, guess_len, B * 4);
+        memcpy(e->h_stage + off_slot, answer_slot, B * 4);
+        if (exact) memcpy(e->h_stage + off_exact, exact, B);
+        k_idx = (const int32_t *)e->h_stage;
+        k_len = (const int32_t *)(e->h_stage + off_len);
+        k_slot = (const int32_t *)(e->h_stage + off_slot);
+        k_exact = exact ? e->h_stage + off_exact : nullptr;
+    }
+    if (!out_pinned) {
+        k_scores = (float *)(e->h_stage + off_scores);
+        k_centi = centi ? (int32_t *)(e->h_stage + off_centi) : nullptr;
+    }
+    if (int rc = cm::enqueue_score(e, k_idx, k_len, n_guesses, n_slots, k_slot, k_exact, min_score,
+                                   k_scores, k_centi, 0u, e->stream))
+        return rc;
     CM_CUDA(cudaStreamSynchronize(e->stream));
-    memcpy(scores, e->h_stage + off_scores, B * 4);
-    if (centi) memcpy(centi, e->h_stage + off_centi, B * 4);
+    if (!out_pinned) {
+        memcpy(scores, k_scores, B * 4);
+        if (centi) memcpy(centi, k_centi, B * 4);
+    }
     return CM_OK;
 }
 

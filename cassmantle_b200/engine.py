@@ -136,3 +136,58 @@ class ScoringEngine:
             self._h, d_guess_idx, d_guess_len, n_guesses, n_slots, d_answer_slot,
             d_exact or None, ctypes.c_float(np.float32(min_score)), d_scores, d_centi or None,
             flags, self._stream(stream) or None))
+
+
+class ScoringPipe:
+    """Ring of page-locked batch slots on one engine (C ABI: cm_pipe_*).
+
+    ``buffers(slot, B, N)`` returns numpy views INTO the slot's pinned block; fill them in
+    place, ``submit(slot, min_score)``, carry on with other slots, then ``wait(slot)`` and read
+    ``scores`` from the same views.  Several slots in flight overlap the input DMA of one batch
+    with the scoring of another.
+    """
+
+    def __init__(self, engine: ScoringEngine, depth: int = 4, max_guesses: int = 4096,
+                 max_slots: int = 16) -> None:
+        self._lib = engine._lib
+        self.engine = engine
+        self._h = ctypes.c_void_p()
+        check(self._lib.cm_pipe_create(ctypes.byref(self._h), engine._h, depth, max_guesses, max_slots))
+        self.depth = depth
+
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.cm_pipe_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self) -> None:  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def buffers(self, slot: int, n_guesses: int, n_slots: int) -> dict:
+        ptrs = [ctypes.c_void_p() for _ in range(6)]
+        check(self._lib.cm_pipe_buffers(self._h, slot, n_guesses, n_slots,
+                                        *[ctypes.byref(p) for p in ptrs]))
+
+        def view(p, ctype, shape):
+            n = int(np.prod(shape))
+            return np.ctypeslib.as_array((ctype * n).from_address(p.value)).reshape(shape)
+
+        B, N = n_guesses, n_slots
+        return {
+            "guess_idx": view(ptrs[0], ctypes.c_int32, (B, N)),
+            "guess_len": view(ptrs[1], ctypes.c_int32, (B,)),
+            "answer_slot": view(ptrs[2], ctypes.c_int32, (B,)),
+            "exact": view(ptrs[3], ctypes.c_uint8, (B,)),
+            "scores": view(ptrs[4], ctypes.c_float, (B,)),
+            "centi": view(ptrs[5], ctypes.c_int32, (B,)),
+        }
+
+    def submit(self, slot: int, min_score: float, want_centi: bool = False) -> None:
+        check(self._lib.cm_pipe_submit(self._h, slot, ctypes.c_float(np.float32(min_score)),
+                                       1 if want_centi else 0))
+
+    def wait(self, slot: int) -> None:
+        check(self._lib.cm_pipe_wait(self._h, slot))

@@ -31,6 +31,7 @@ extern "C" {
 #endif
 
 typedef struct cm_engine cm_engine;
+typedef struct cm_pipe cm_pipe;
 
 typedef enum cm_status {
     CM_OK = 0,
@@ -111,12 +112,38 @@ int cm_score_batch_device(cm_engine *e,
 
 /* Same call with HOST buffers: stages the inputs to the GPU, scores, copies the results
  * back and returns when `scores` (and `centi`, if not NULL) are valid.  This is what the
- * Python boundary (cassmantle_b200/backend.py) calls per micro-batch.                     */
+ * Python boundary (cassmantle_b200/backend.py) calls per micro-batch.  Page-locked
+ * buffers (cudaHostAlloc / cudaHostRegister, e.g. torch pin_memory) are read and written
+ * by the kernel directly; pageable ones go through one pinned staging block.             */
 int cm_score_batch_host(cm_engine *e,
                         const int32_t *guess_idx, const int32_t *guess_len,
                         int n_guesses, int n_slots,
                         const int32_t *answer_slot, const uint8_t *exact,
                         float min_score, float *scores, int32_t *centi);
+
+/* ---- pipelined host path --------------------------------------------------------------- *
+ * No reference counterpart: the reference scores one request at a time inside its event
+ * loop (src/backend.py:312-317).  This is the device half of the request micro-batcher that
+ * north_star adds to src/server.py.  A pipe is a ring of `depth` slots; each slot owns a
+ * page-locked host block that the caller fills IN PLACE, so a step costs one DMA of the
+ * packed inputs, one kernel, and no copy back (the kernel writes scores into the block).
+ *
+ *   cm_pipe_buffers(p, s, B, N, &idx, &len, &slot, &exact, &scores, &centi)   fill these
+ *   cm_pipe_submit(p, s, min_score, want_centi)                                asynchronous
+ *   ... fill and submit other slots ...
+ *   cm_pipe_wait(p, s)                                   scores[0..B) (and centi) are valid
+ *
+ * Every entry of exact[] must be written (0 or 1).  Answers must be registered and complete
+ * (cm_set_answers + cm_engine_synchronize, or the same stream order) before a submit, and
+ * must not be changed while any slot is in flight.  Not thread-safe per pipe.              */
+int cm_pipe_create(cm_pipe **out, cm_engine *e, int depth, int max_guesses, int max_slots);
+int cm_pipe_destroy(cm_pipe *p);
+int cm_pipe_depth(cm_pipe *p);
+int cm_pipe_buffers(cm_pipe *p, int slot, int n_guesses, int n_slots,
+                    int32_t **guess_idx, int32_t **guess_len, int32_t **answer_slot,
+                    uint8_t **exact, float **scores, int32_t **centi);
+int cm_pipe_submit(cm_pipe *p, int slot, float min_score, int want_centi);
+int cm_pipe_wait(cm_pipe *p, int slot);
 
 /* Number of kernels this library has launched since it was loaded (bench.py reports it). */
 int64_t cm_kernel_launch_count(void);

@@ -174,6 +174,47 @@ def test_overlapped_launches_match_serial(small_engine):
         assert np.array_equal(outs[i].cpu().numpy().view(np.uint32), want[i].view(np.uint32)), i
 
 
+def test_pipe_matches_host_entry_point(small_engine):
+    """cm_pipe_*: slots filled in place, several in flight, results bit-identical to the
+    synchronous host call; shapes may differ from slot to slot and slots are reusable."""
+    from cassmantle_b200._lib import CassMantleError
+    from cassmantle_b200.engine import ScoringPipe
+    ans = np.array([7, 4242, 31337], np.int32)
+    small_engine.set_answers(ans)
+    small_engine.synchronize()
+    pipe = ScoringPipe(small_engine, depth=3, max_guesses=2048, max_slots=16)
+    shapes = [(2048, 16), (100, 1), (777, 5), (2048, 1), (1, 16), (640, 8), (333, 3)]
+    inflight = {}
+    want = {}
+    for i, (B, N) in enumerate(shapes):
+        s = i % 3
+        if s in inflight:
+            pipe.wait(s)
+            j, v = inflight.pop(s)
+            assert np.array_equal(v["scores"].view(np.uint32), want[j][0].view(np.uint32)), j
+            assert np.array_equal(v["centi"], want[j][1]), j
+        idx, ln, _, slot, ex = synth.make_guess_batch(B, N, 50_000, 3, seed=500 + i, ragged=N > 1)
+        want[i] = small_engine.score_host(idx, ln, slot, ex, 0.01, want_centi=True)
+        v = pipe.buffers(s, B, N)
+        v["guess_idx"][:] = idx
+        v["guess_len"][:] = ln
+        v["answer_slot"][:] = slot
+        v["exact"][:] = ex
+        v["scores"][:] = -1.0
+        pipe.submit(s, 0.01, want_centi=True)
+        inflight[s] = (i, v)
+        with pytest.raises(CassMantleError):
+            pipe.buffers(s, B, N)              # the slot is busy until it has been waited for
+    for s, (j, v) in inflight.items():
+        pipe.wait(s)
+        assert np.array_equal(v["scores"].view(np.uint32), want[j][0].view(np.uint32)), j
+    with pytest.raises(CassMantleError):
+        pipe.buffers(0, 4096, 16)              # beyond max_guesses
+    with pytest.raises(CassMantleError):
+        pipe.buffers(5, 16, 16)                # no such slot
+    pipe.close()
+
+
 # ---------------------------------------------------------------------------------------
 # edge cases the reference's semantics define
 # ---------------------------------------------------------------------------------------
