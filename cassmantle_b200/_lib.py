@@ -20,6 +20,7 @@ CM_MAX_DIM = 1024
 CM_MAX_ANSWERS = 4096
 CM_MAX_SEQ = 4096
 CM_SCORE_OVERLAP_PREVIOUS = 0x1
+CM_NOALLOC_MAX_ANSWERS = 64
 
 
 class CassMantleError(RuntimeError):
@@ -54,6 +55,8 @@ _SIGNATURES = {
     "cm_pipe_buffers": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_int] + [_c.POINTER(_P)] * 6),
     "cm_pipe_submit": (_c.c_int, [_P, _c.c_int, _c.c_float, _c.c_int]),
     "cm_pipe_wait": (_c.c_int, [_P, _c.c_int]),
+    "cm_score_batch_noalloc": (_c.c_int, [_c.c_int, _P, _c.c_int64, _c.c_int, _P, _c.c_int, _P, _P,
+                                          _c.c_int, _c.c_int, _P, _P, _c.c_float, _P, _P, _P]),
     "cm_score_batch_host": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _P, _P, _c.c_float,
                                        _P, _P]),
 }

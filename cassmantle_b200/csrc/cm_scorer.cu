@@ -691,3 +691,108 @@ int cm_score_batch_host(cm_engine *e, const int32_t *guess_idx, const int32_t *g
 }
 
 }  // extern "C"
+
+// ======================================================================================
+// cm_score_batch_noalloc -- scoring for callers that are not allowed to allocate.
+//
+// Who needs it: a host program that has given every byte of GPU memory to an allocator of
+// its own (a serving framework's arena, a memory plan fixed at start-up, a tensor library
+// that owns the table), or one that must keep cudaMalloc's device-wide synchronisation out
+// of its request path.  Such a caller cannot create a cm_engine, because the engine
+// allocates the table replica and the answers' unit vectors.  Here the caller brings the
+// table, the batch and the output buffers; the only memory the library adds is the fixed
+// array below, which is part of the loaded module on every GPU until the process exits.
+//
+// The scratch holds unitvec(table[answer_rows[a]]) for a < n_answers -- exactly what
+// cm_set_answers keeps in engine memory -- so its size bounds the call:
+//   n_answers <= CM_NOALLOC_MAX_ANSWERS (64) and dim <= CM_MAX_DIM (1024): 256 KiB.
+// Each call first rewrites rows [0, n_answers) in full (an unknown answer gets zeros) and
+// reads nothing else, so nothing has to start at zero and stale rows from an earlier call
+// are never seen.  All calls share the one array: two calls whose kernels can overlap on the
+// GPU (different streams, no ordering between them) race on it -- keep them on one stream or
+// order them with events.
+//
+// In host code the name `g_noalloc_scratch` is only a handle for the symbol, not a device
+// address.  The address is looked up with cudaGetSymbolAddress once per device, with that
+// device current, the first time the entry point is used on it; make that first call before
+// any stream capture begins.
+// ======================================================================================
+static __device__ __align__(256) float g_noalloc_scratch[CM_NOALLOC_MAX_ANSWERS * CM_MAX_DIM];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+float *g_noalloc_ptr[kMaxDevices] = {};
+
+// Device address of the scratch array on `device` (which must be current).
+int noalloc_scratch_address(int device, float **out) {
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_ptr[device] == nullptr) {
+        float *p = nullptr;
+        cudaError_t err = cudaGetSymbolAddress((void **)&p, g_noalloc_scratch);
+        if (err != cudaSuccess || p == nullptr) {
+            cudaGetLastError();
+            return fail(CM_ERR_CUDA, "cudaGetSymbolAddress(scratch) on device %d failed: %s", device,
+                        cudaGetErrorString(err));
+        }
+        g_noalloc_ptr[device] = p;
+    }
+    *out = g_noalloc_ptr[device];
+    return CM_OK;
+}
+
+}  // namespace
+
+extern "C" int cm_score_batch_noalloc(int device, const float *d_table, int64_t n_rows, int dim,
+                                      const int32_t *d_answer_rows, int n_answers,
+                                      const int32_t *d_guess_idx, const int32_t *d_guess_len,
+                                      int n_guesses, int n_slots, const int32_t *d_answer_slot,
+                                      const uint8_t *d_exact, float min_score, float *d_scores,
+                                      int32_t *d_centi, void *stream) {
+    if (device < 0 || device >= kMaxDevices)
+        return fail(CM_ERR_INVALID, "device %d outside [0, %d)", device, kMaxDevices);
+    if (n_rows <= 0 || n_rows > 0x7fffffffLL)
+        return fail(CM_ERR_INVALID, "n_rows %lld outside [1, 2^31)", (long long)n_rows);
+    if (dim < 4 || dim > CM_MAX_DIM || dim % 4 != 0)
+        return fail(CM_ERR_INVALID, "dim %d must be a multiple of 4 in [4, %d]", dim, CM_MAX_DIM);
+    if (n_answers < 1 || n_answers > CM_NOALLOC_MAX_ANSWERS)
+        return fail(CM_ERR_INVALID,
+                    "n_answers %d outside [1, %d]: the fixed scratch array holds at most %d answer "
+                    "vectors; use a cm_engine for more", n_answers, CM_NOALLOC_MAX_ANSWERS,
+                    CM_NOALLOC_MAX_ANSWERS);
+    if (n_guesses < 0) return fail(CM_ERR_INVALID, "n_guesses %d is negative", n_guesses);
+    if (n_slots < 1 || n_slots > CM_MAX_SEQ)
+        return fail(CM_ERR_INVALID, "n_slots %d outside [1, %d]", n_slots, CM_MAX_SEQ);
+    if (!d_table || !d_answer_rows) return fail(CM_ERR_INVALID, "table or answer_rows is NULL");
+    if (n_guesses == 0) return CM_OK;
+    if (!d_guess_idx || !d_guess_len || !d_answer_slot || !d_scores)
+        return fail(CM_ERR_INVALID, "a required buffer pointer is NULL");
+
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(CM_ERR_CUDA, "cudaSetDevice(%d) failed", device);
+    float *scratch = nullptr;
+    if (int rc = noalloc_scratch_address(device, &scratch)) return rc;
+
+    // A borrowed, stack-only view in the shape the launchers expect: the caller's table and
+    // answer rows, the static array for the unit vectors.  Nothing here owns memory.
+    cm_engine view;
+    view.device = device;
+    view.n_rows = n_rows;
+    view.dim = dim;
+    view.d_table = const_cast<float *>(d_table);
+    view.d_ans_unit = scratch;
+    view.d_ans_rows = const_cast<int32_t *>(d_answer_rows);
+    view.n_answers = n_answers;
+    cudaStream_t st = (cudaStream_t)stream;
+#define CM_CALL(V) launch_answers<V>(&view, d_answer_rows, n_answers, st)
+    CM_DISPATCH_VPL(dim, CM_CALL)
+#undef CM_CALL
+    CM_CUDA(cudaGetLastError());
+#define CM_CALL(V) launch_score<V>(&view, d_guess_idx, d_guess_len, n_guesses, n_slots, d_answer_slot, \
+                                   d_exact, min_score, d_scores, d_centi, 0u, st)
+    CM_DISPATCH_VPL(dim, CM_CALL)
+#undef CM_CALL
+    CM_CUDA(cudaGetLastError());
+    return CM_OK;
+}

@@ -145,6 +145,31 @@ int cm_pipe_buffers(cm_pipe *p, int slot, int n_guesses, int n_slots,
 int cm_pipe_submit(cm_pipe *p, int slot, float min_score, int want_centi);
 int cm_pipe_wait(cm_pipe *p, int slot);
 
+/* ---- scoring without any allocation ---------------------------------------------------- *
+ * No counterpart in the reference.  For callers that must not allocate GPU memory: programs
+ * whose device memory belongs entirely to their own allocator or to a memory plan fixed at
+ * start-up, and request paths that cannot afford cudaMalloc's device-wide synchronisation.
+ * They cannot use a cm_engine (it allocates the table replica and the answers' unit
+ * vectors), so this call takes everything from the caller: the fp32 table already on
+ * `device` (n_rows x dim, row-major), the answers' table rows as a DEVICE array, the batch
+ * and the outputs.  Semantics and arguments are otherwise those of cm_set_answers_device
+ * followed by cm_score_batch_device with flags 0, and results are identical.
+ * The unit vectors of the answers live in one fixed array inside the library
+ * (CM_NOALLOC_MAX_ANSWERS x CM_MAX_DIM floats = 256 KiB, resident on every GPU that loads the
+ * library until the process exits); n_answers above CM_NOALLOC_MAX_ANSWERS or dim above
+ * CM_MAX_DIM is rejected with CM_ERR_INVALID.  The call performs no cudaMalloc/cudaFree.
+ * The first call on a device looks the array's address up (once per device): make that
+ * first call before any stream capture.  All calls share the array and each rewrites the
+ * part it uses, so calls that may overlap on the GPU (different streams, unordered) race --
+ * keep them on one stream or order them.  Asynchronous on `stream`.                         */
+#define CM_NOALLOC_MAX_ANSWERS 64
+int cm_score_batch_noalloc(int device, const float *d_table, int64_t n_rows, int dim,
+                           const int32_t *d_answer_rows, int n_answers,
+                           const int32_t *d_guess_idx, const int32_t *d_guess_len,
+                           int n_guesses, int n_slots,
+                           const int32_t *d_answer_slot, const uint8_t *d_exact,
+                           float min_score, float *d_scores, int32_t *d_centi, void *stream);
+
 /* Number of kernels this library has launched since it was loaded (bench.py reports it). */
 int64_t cm_kernel_launch_count(void);
 
