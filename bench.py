@@ -55,13 +55,12 @@ WORKLOAD = (f"{B} guesses x {N} word slots per step, resident table {V}x{D} fp32
 
 
 def make_ring(seed0: int):
+    """RING batches of guesses seeded by `seed0` (per rank); the round's answers are the same
+    on every rank and for every batch: one round, the answers stay, the guesses change."""
+    ans = np.random.default_rng(999).choice(V, size=N_ANSWERS, replace=False).astype(np.int32)
     ring = []
-    ans = None
     for i in range(RING):
-        idx, ln, a, slot, ex = synth.make_guess_batch(B, N, V, N_ANSWERS, seed=seed0 + i,
-                                                      near_frac=0.3 if i == 0 else 0.0)
-        if ans is None:
-            ans = a                      # one round: the answers stay, the guesses change
+        idx, ln, _, slot, ex = synth.make_guess_batch(B, N, V, N_ANSWERS, seed=seed0 + i, near_frac=0.0)
         ring.append((idx, ln, slot, ex))
     return ans, ring
 
@@ -266,18 +265,34 @@ def run_own(args) -> None:
     st = stream.cuda_stream
     assert st != 0
 
-    def step_device(i: int) -> None:
-        t = d_ring[i % RING]
-        eng.score_device(t[0].data_ptr(), t[1].data_ptr(), B, N, t[2].data_ptr(), t[3].data_ptr(),
-                         MIN_SCORE, d_scores.data_ptr(), 0, stream=st, flags=OVERLAP)
-        if world > 1:        # north_star: per-guess scores are all-gathered over NVLink
-            dist.all_gather_into_tensor(gathered, d_scores)
+    gather = None
+    if world > 1 and args.collective == "fused":
+        from cassmantle_b200.dist import ScoreGather
+        gather = ScoreGather(eng, B, depth=4)
+        gather.exchange_handles()
+        dist.barrier()
+
+    import ctypes
+    ms32 = ctypes.c_float(np.float32(MIN_SCORE))
+    t_ring = [(t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(), t[3].data_ptr()) for t in d_ring]
+    score_dev, score_gather = lib.cm_score_batch_device, lib.cm_score_batch_gather
+    eh, out_p = eng._h, d_scores.data_ptr()
+    gh = gather._h if gather is not None else None
+
+    def step_device(i: int) -> None:        # the raw C-ABI calls: keep Python out of the timed loop
+        p = t_ring[i % RING]
+        if gh is not None:   # scoring launch + exchange kernel: every rank ends up with all scores
+            rc = score_gather(eh, gh, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
+        else:
+            rc = score_dev(eh, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
+            if world > 1:    # --collective nccl: a separate all-gather per step
+                dist.all_gather_into_tensor(gathered, d_scores)
+        if rc != 0:
+            _lib.check(rc)
 
     h_np = [tuple(t.numpy() for t in tup) for tup in h_ring]
     h_scores_np = h_scores.numpy()
     score_host = lib.cm_score_batch_host
-    import ctypes
-    ms32 = ctypes.c_float(np.float32(MIN_SCORE))
 
     def step_host(i: int) -> None:
         a = h_np[i % RING]
@@ -308,19 +323,38 @@ def run_own(args) -> None:
     launches0 = lib.cm_kernel_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
+    t_enq = time.perf_counter()
     for i in range(args.steps):
         step_device(args.warmup + i)
     e1.record(stream)
+    t_enq = time.perf_counter() - t_enq
     barrier()
     gpu_launches = int(lib.cm_kernel_launch_count() - launches0)
     dev_ms = max_over_ranks(e0.elapsed_time(e1))
     value = args.steps * B * world / (dev_ms * 1e-3)
 
+    # every rank must now hold every rank's scores of the last step (checked against a local
+    # re-score of the peers' batches, which are seeded by rank)
+    gather_check = None
+    if gather is not None:
+        ptr = gather.wait(st)          # ships the last step (no launch follows it) and waits for all ranks
+        torch.cuda.synchronize()
+        got = gather.as_tensor(ptr).cpu().numpy()
+        last = (args.warmup + args.steps - 1) % RING
+        ok = gather.timed_out() == 0
+        for r in range(world):
+            _, ring_r = make_ring(1000 + 7919 * r)
+            idx_r, ln_r, slot_r, ex_r = ring_r[last]
+            want_r, _ = eng.score_host(idx_r, ln_r, slot_r, ex_r, MIN_SCORE)
+            ok = ok and bool(np.array_equal(got[r, :B].view(np.uint32), want_r.view(np.uint32)))
+        t_ok = torch.tensor([1.0 if ok else 0.0], device=dev)
+        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+        gather_check = bool(t_ok.item() == 1.0)
+
     # ---- roofline: the scoring kernel alone, >= ~1 s of launches -------------------------
     per_step_ms = max(dev_ms / args.steps, 1e-3)
     n_roof = int(min(200_000, max(2000, args.roofline_s * 1e3 / per_step_ms)))
-    t_ring = [(t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(), t[3].data_ptr()) for t in d_ring]
-    fn, h, out_p = lib.cm_score_batch_device, eng._h, d_scores.data_ptr()
+    fn, h = lib.cm_score_batch_device, eng._h
     for i in range(50):
         p = t_ring[i % RING]
         fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
@@ -438,15 +472,22 @@ def run_own(args) -> None:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+            "host_enqueue_ms_per_step": t_enq / args.steps * 1e3,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "guesses_per_step_per_gpu": B, "word_slots": N,
                        "parallelism": f"replica-per-gpu x{world}, batch sharded, "
-                                      + ("NCCL all_gather of scores" if world > 1 else "no collective"),
+                                      + (("scores of every step all-gathered over NVLink peer stores by a ship CTA riding in the next scoring launch (cm_score_batch_gather)"
+                                          if gather is not None else "NCCL all_gather of scores")
+                                         if world > 1 else "no collective"),
+                       "gather_verified": gather_check,
                        "l2": f"ring of {RING} distinct batches over a 3.6 GB table (inputs >> L2)"},
             "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
             "cpu_baseline": cpu_baseline, "clocks": clocks, "latency": lat, "parity": parity,
         }
         print(json.dumps(line), flush=True)
+    if gather is not None:
+        dist.barrier()
+        gather.close()
     eng.close()
     if world > 1:
         dist.destroy_process_group()
@@ -468,6 +509,7 @@ def main() -> None:
     ap.add_argument("--ref-budget-s", type=float, default=60.0)
     ap.add_argument("--roofline-s", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--collective", default="fused", choices=["fused", "nccl"])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

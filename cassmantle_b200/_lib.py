@@ -21,6 +21,7 @@ CM_MAX_ANSWERS = 4096
 CM_MAX_SEQ = 4096
 CM_SCORE_OVERLAP_PREVIOUS = 0x1
 CM_NOALLOC_MAX_ANSWERS = 64
+CM_GATHER_DEFER_WAIT = 0x2
 
 
 class CassMantleError(RuntimeError):
@@ -55,6 +56,19 @@ _SIGNATURES = {
     "cm_pipe_buffers": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_int] + [_c.POINTER(_P)] * 6),
     "cm_pipe_submit": (_c.c_int, [_P, _c.c_int, _c.c_float, _c.c_int]),
     "cm_pipe_wait": (_c.c_int, [_P, _c.c_int]),
+    "cm_gather_create": (_c.c_int, [_c.POINTER(_P), _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int]),
+    "cm_gather_destroy": (_c.c_int, [_P]),
+    "cm_gather_export": (_c.c_int, [_P, _P]),
+    "cm_gather_import": (_c.c_int, [_P, _c.c_int, _P]),
+    "cm_gather_import_ptr": (_c.c_int, [_P, _c.c_int, _P]),
+    "cm_gather_block": (_c.c_int, [_P, _c.POINTER(_P), _c.POINTER(_c.c_int64)]),
+    "cm_gather_stride": (_c.c_int, [_P]),
+    "cm_score_batch_gather": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _P, _P, _c.c_float,
+                                         _P, _P, _c.c_uint32, _P]),
+    "cm_gather_result": (_c.c_int, [_P, _c.POINTER(_P)]),
+    "cm_gather_flush": (_c.c_int, [_P, _P]),
+    "cm_gather_wait": (_c.c_int, [_P, _c.POINTER(_P), _P]),
+    "cm_gather_status": (_c.c_int, [_P, _c.POINTER(_c.c_int)]),
     "cm_score_batch_noalloc": (_c.c_int, [_c.c_int, _P, _c.c_int64, _c.c_int, _P, _c.c_int, _P, _P,
                                           _c.c_int, _c.c_int, _P, _P, _c.c_float, _P, _P, _P]),
     "cm_score_batch_host": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _P, _P, _c.c_float,

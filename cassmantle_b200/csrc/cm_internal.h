@@ -6,6 +6,7 @@
 #include <mutex>
 
 #include "../../include/cassmantle_b200.h"
+#include "cm_ship.cuh"
 
 struct cm_engine {
     int device = 0;
@@ -56,9 +57,11 @@ bool is_pinned_host(const void *p);
 int check_engine(const cm_engine *e);
 
 // Validates the arguments and enqueues the scoring kernel; pointers may be device memory or
-// pinned host memory (the kernel then reads / writes it across PCIe itself).
+// pinned host memory (the kernel then reads / writes it across PCIe itself).  `ship`, if not
+// NULL, adds CTAs to the launch that ship an EARLIER step's scores to the other ranks.
 int enqueue_score(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_len, int n_guesses,
                   int n_slots, const int32_t *answer_slot, const uint8_t *exact, float min_score,
-                  float *scores, int32_t *centi, uint32_t flags, cudaStream_t st);
+                  float *scores, int32_t *centi, uint32_t flags, cudaStream_t st,
+                  const ShipArgs *ship = nullptr);
 
 }  // namespace cm

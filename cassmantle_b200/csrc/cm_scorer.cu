@@ -167,15 +167,16 @@ cm_answer_unit_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
 //   phase 2  / N, unitvec through an fp64 norm, fp32 dot with the answer's unit vector,
 //            floor at min_score, optional hundredths of a percent
 // --------------------------------------------------------------------------------------
-template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE>
-__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
-cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
-                const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
-                int n_guesses, int n_slots,
-                const float *__restrict__ ans_unit, const int32_t *__restrict__ ans_rows,
-                int n_answers, const int32_t *__restrict__ answer_slot,
-                const uint8_t *__restrict__ exact, float min_score,
-                float *__restrict__ scores, int32_t *__restrict__ centi, uint32_t flags) {
+template <int VPL, int LPG, int R, bool STREAM, int THREADS, bool SINGLE>
+__device__ __forceinline__ void
+score_groups(const float *__restrict__ table, int64_t n_rows, int dim4,
+             const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
+             int n_guesses, int n_slots,
+             const float *__restrict__ ans_unit, const int32_t *__restrict__ ans_rows,
+             int n_answers, const int32_t *__restrict__ answer_slot,
+             const uint8_t *__restrict__ exact, float min_score,
+             float *__restrict__ scores, int32_t *__restrict__ centi, uint32_t flags,
+             int first_cta) {
     constexpr int G = 32 / LPG;
     // Programmatic dependent launch: let the next launch on the stream start scheduling now,
     // and unless the caller vouched for the inputs (CM_SCORE_OVERLAP_PREVIOUS) wait for the
@@ -186,7 +187,7 @@ cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
     const int lane = threadIdx.x & 31;
     const int sub = lane & (LPG - 1);
     const int grp_base = lane & ~(LPG - 1);
-    const int warp = blockIdx.x * (THREADS / 32) + (threadIdx.x >> 5);
+    const int warp = ((int)blockIdx.x - first_cta) * (THREADS / 32) + (threadIdx.x >> 5);
     const int b_raw = warp * G + lane / LPG;
     if (warp * G >= n_guesses) return;                      // whole warp out of range
     const bool have = b_raw < n_guesses;
@@ -309,6 +310,29 @@ cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
     }
 }
 
+template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
+                const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
+                int n_guesses, int n_slots,
+                const float *__restrict__ ans_unit, const int32_t *__restrict__ ans_rows,
+                int n_answers, const int32_t *__restrict__ answer_slot,
+                const uint8_t *__restrict__ exact, float min_score,
+                float *__restrict__ scores, int32_t *__restrict__ centi, uint32_t flags,
+                int n_ship_ctas, const cm::ShipArgs ship) {
+    // Several GPUs (cm_gather.cu): the first `n_ship_ctas` CTAs do not score -- they ship the
+    // PREVIOUS step's scores to the other ranks while the rest of the launch gathers its rows.
+    // (First, because CTAs are dispatched in index order and the ship should start at once.)
+    if ((int)blockIdx.x < n_ship_ctas) {
+        cm::pdl_launch_dependents();
+        cm::ship_duty(ship, (int)blockIdx.x, n_ship_ctas);
+        return;
+    }
+    score_groups<VPL, LPG, R, STREAM, THREADS, SINGLE>(
+        table, n_rows, dim4, guess_idx, guess_len, n_guesses, n_slots, ans_unit, ans_rows, n_answers,
+        answer_slot, exact, min_score, scores, centi, flags, n_ship_ctas);
+}
+
 }  // namespace
 
 namespace {
@@ -319,10 +343,13 @@ namespace {
 template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE = false>
 void launch_variant(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
                     const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
-                    int32_t *centi, uint32_t flags, cudaStream_t st) {
+                    int32_t *centi, uint32_t flags, cudaStream_t st, const cm::ShipArgs *ship) {
     constexpr int per_cta = (THREADS / 32) * (32 / LPG);
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)((B + per_cta - 1) / per_cta));
+    const int score_ctas = (B + per_cta - 1) / per_cta;
+    const bool shipping = ship != nullptr && ship->world > 0;
+    const int n_ship_ctas = shipping ? cm::ship_ctas(ship->n) : 0;
+    cfg.gridDim = dim3((unsigned)(score_ctas + n_ship_ctas));
     cfg.blockDim = dim3(THREADS);
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
@@ -333,7 +360,8 @@ void launch_variant(const cm_engine *e, const int32_t *gi, const int32_t *gl, in
     cudaLaunchKernelEx(&cfg, cm_score_kernel<VPL, LPG, R, STREAM, THREADS, MIN_BLOCKS, SINGLE>,
                        (const float *)e->d_table, e->n_rows, e->dim / 4, gi, gl, B, N,
                        (const float *)e->d_ans_unit, (const int32_t *)e->d_ans_rows, e->n_answers,
-                       slot, exact, min_score, scores, centi, flags);
+                       slot, exact, min_score, scores, centi, flags, n_ship_ctas,
+                       shipping ? *ship : cm::ShipArgs{});
     cm::count_launch();
 }
 
@@ -348,11 +376,11 @@ int forced_variant() {
 template <int VPL>
 void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
                   const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
-                  int32_t *centi, uint32_t flags, cudaStream_t st) {
+                  int32_t *centi, uint32_t flags, cudaStream_t st, const cm::ShipArgs *ship = nullptr) {
 #define CM_V(LPG, R, STREAM, THREADS, MINB, VP) \
-    launch_variant<VP, LPG, R, STREAM, THREADS, MINB>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st)
+    launch_variant<VP, LPG, R, STREAM, THREADS, MINB>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st, ship)
 #define CM_S(LPG, STREAM, THREADS, MINB, VP) \
-    launch_variant<VP, LPG, 1, STREAM, THREADS, MINB, true>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st)
+    launch_variant<VP, LPG, 1, STREAM, THREADS, MINB, true>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st, ship)
     if constexpr (VPL == 3) {
         if (e->dim == 300) {
             int variant = forced_variant();
@@ -429,7 +457,7 @@ bool is_pinned_host(const void *p) {
 
 int enqueue_score(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_len, int n_guesses,
                   int n_slots, const int32_t *answer_slot, const uint8_t *exact, float min_score,
-                  float *scores, int32_t *centi, uint32_t flags, cudaStream_t st) {
+                  float *scores, int32_t *centi, uint32_t flags, cudaStream_t st, const ShipArgs *ship) {
     if (int rc = check_engine(e)) return rc;
     if (n_guesses < 0) return fail(CM_ERR_INVALID, "n_guesses %d is negative", n_guesses);
     if (n_slots < 1 || n_slots > CM_MAX_SEQ)
@@ -442,7 +470,7 @@ int enqueue_score(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_l
     if (e->n_answers < 1) return fail(CM_ERR_STATE, "cm_set_answers has not been called");
     DeviceGuard guard(e->device);
 #define CM_CALL(V) launch_score<V>(e, guess_idx, guess_len, n_guesses, n_slots, answer_slot, exact, \
-                                   min_score, scores, centi, flags, st)
+                                   min_score, scores, centi, flags, st, ship)
     CM_DISPATCH_VPL(e->dim, CM_CALL)
 #undef CM_CALL
     CM_CUDA(cudaGetLastError());

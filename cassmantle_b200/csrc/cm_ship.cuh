@@ -1,0 +1,120 @@
+// Device side of the score all-gather (see cm_gather.cu for the protocol and its rationale).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace cm {
+
+constexpr int kMaxPeers = 8;
+constexpr uint32_t kShipSentinel = 0xffffffffu;   // a NaN pattern no score can be (NaN -> min_score)
+constexpr int kShipChunk = 4096;                  // scores handled by one ship CTA
+
+// Work order for the CTAs that ship ONE finished step of scores to every rank.  world == 0: none.
+struct ShipArgs {
+    float *dst[kMaxPeers];        // rank r's receive buffer of that step: [world][stride] floats
+    uint32_t *flag[kMaxPeers];    // rank r's flag array [world]; flag[r][me] = last step I shipped
+    const uint32_t *my_flags;     // my own flag array
+    uint32_t *stage;              // local staging slot of that step (scores or sentinel)
+    float *copy_to;               // optional: a caller buffer that also receives my scores
+    unsigned *counter;            // CTA arrival counter (only touched when several CTAs ship)
+    int *err;                     // 0, or who timed out
+    long long timeout_cycles;
+    uint32_t step;
+    int world, rank, stride, n, spin;
+};
+
+__host__ __device__ inline int ship_ctas(int n) { return n > 0 ? (n + kShipChunk - 1) / kShipChunk : 1; }
+
+__device__ __forceinline__ void spin_on_flags(const uint32_t *flags, int world, uint32_t step,
+                                              long long timeout_cycles, int *err) {
+    const int r = threadIdx.x;
+    if (r >= world) return;
+    const long long t0 = clock64();
+    for (;;) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + r) : "memory");
+        if ((int32_t)(v - step) >= 0) break;
+        if (clock64() - t0 > timeout_cycles) {          // a peer died or never launched: do not hang
+            atomicExch(err, r + 1);
+            break;
+        }
+        __nanosleep(100);
+    }
+}
+
+// Executed by `n_ctas` whole CTAs (index `cta`), any block size that is a multiple of 32.
+//  0. wait until this rank has published step-1 (ships are strictly ordered)
+//  1. poll the staging slot until no sentinel is left in my chunk: the data is the flag, so the
+//     scoring launch needs no fence, atomic or tail of its own
+//  2. copy the scores into every rank's receive buffer (16-byte stores through peer mappings),
+//     optionally into the caller's buffer, and reset the slot to the sentinel
+//  3. fence.sys; the last CTA publishes the step in my entry of every peer's flag array
+//  4. unless deferred, wait (bounded) until every rank's flag in MY array has reached the step
+__device__ __forceinline__ void ship_duty(const ShipArgs &a, int cta, int n_ctas) {
+    __shared__ int s_last;
+    const int lo = cta * kShipChunk;
+    const int hi = min(a.n, lo + kShipChunk);
+    const long long t0 = clock64();
+    // 0. ships run strictly in step order.  A ship CTA does not honour the grid dependency of
+    //    its launch, so with short kernels the ship of step s+depth can be resident before step
+    //    s has been shipped -- and both use the same staging slot.  My own entry of my flag
+    //    array says which step I published last: wait until it is step-1.
+    if (threadIdx.x == 0) {
+        for (;;) {
+            uint32_t v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(a.my_flags + a.rank) : "memory");
+            if ((int32_t)(v - (a.step - 1u)) >= 0) break;
+            if (clock64() - t0 > a.timeout_cycles) {
+                atomicExch(a.err, -(int)a.step);
+                break;
+            }
+            __nanosleep(100);
+        }
+    }
+    __syncthreads();
+    for (int i = lo + 4 * (int)threadIdx.x; i < hi; i += 4 * (int)blockDim.x) {
+        for (;;) {
+            uint4 v;
+            asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(a.stage + i) : "memory");
+            const bool pending = v.x == kShipSentinel || (i + 1 < hi && v.y == kShipSentinel) ||
+                                 (i + 2 < hi && v.z == kShipSentinel) || (i + 3 < hi && v.w == kShipSentinel);
+            if (!pending) {
+#pragma unroll
+                for (int r = 0; r < kMaxPeers; ++r)
+                    if (r < a.world)
+                        *reinterpret_cast<uint4 *>(a.dst[r] + (size_t)a.rank * a.stride + i) = v;
+                if (a.copy_to != nullptr) {
+                    a.copy_to[i] = __uint_as_float(v.x);
+                    if (i + 1 < hi) a.copy_to[i + 1] = __uint_as_float(v.y);
+                    if (i + 2 < hi) a.copy_to[i + 2] = __uint_as_float(v.z);
+                    if (i + 3 < hi) a.copy_to[i + 3] = __uint_as_float(v.w);
+                }
+                *reinterpret_cast<uint4 *>(a.stage + i) =
+                    make_uint4(kShipSentinel, kShipSentinel, kShipSentinel, kShipSentinel);
+                break;
+            }
+            if (clock64() - t0 > a.timeout_cycles) {
+                atomicExch(a.err, -(int)a.step);        // the scoring launch of that step never delivered
+                break;
+            }
+            __nanosleep(100);
+        }
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s_last = (n_ctas == 1) || (atomicAdd(a.counter, 1u) == (unsigned)n_ctas - 1u);
+        if (s_last) {
+            if (n_ctas > 1) *a.counter = 0u;
+            __threadfence_system();
+            for (int r = 0; r < a.world; ++r)
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.flag[r] + a.rank), "r"(a.step)
+                             : "memory");
+        }
+    }
+    __syncthreads();
+    if (s_last && a.spin) spin_on_flags(a.my_flags, a.world, a.step, a.timeout_cycles, a.err);
+}
+
+}  // namespace cm

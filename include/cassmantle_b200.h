@@ -32,6 +32,7 @@ extern "C" {
 
 typedef struct cm_engine cm_engine;
 typedef struct cm_pipe cm_pipe;
+typedef struct cm_gather cm_gather;
 
 typedef enum cm_status {
     CM_OK = 0,
@@ -144,6 +145,52 @@ int cm_pipe_buffers(cm_pipe *p, int slot, int n_guesses, int n_slots,
                     uint8_t **exact, float **scores, int32_t **centi);
 int cm_pipe_submit(cm_pipe *p, int slot, float min_score, int want_centi);
 int cm_pipe_wait(cm_pipe *p, int slot);
+
+/* ---- several GPUs: score all-gather over NVLink peer memory ---------------------------- *
+ * No reference counterpart (the reference has no collective).  SURVEY.md §8e: one process
+ * per GPU, a table replica each, every rank scores its slice of the batch and every rank
+ * needs all scores.  That is 4 bytes per guess -- pure latency for a library collective -- so
+ * the exchange rides inside the scoring launches, one step behind: launch s writes its scores
+ * to a staging slot; launch s+1 carries one extra CTA per 4096 scores that copies step s
+ * into every rank's receive buffer through peer mappings, publishes a step flag on every
+ * peer and waits (bounded, ~2 s) for every rank's flag, while the other CTAs already gather
+ * rows for step s+1.  One launch per step; the exchange is never on the critical path.
+ * world <= 8, one node.
+ *
+ *   cm_gather_create(&g, e, rank, world, max_guesses_per_rank, depth)      depth >= 2
+ *   cm_gather_export(g, h)  -> exchange the 64-byte handles -> cm_gather_import(g, r, h_r)
+ *   per step:  cm_score_batch_gather(e, g, ...same arguments as cm_score_batch_device...)
+ *              (d_scores may be NULL; when given it also receives this rank's own scores
+ *               when the step is shipped)
+ *   consumer:  cm_gather_wait(g, &d_all, stream) ships the latest step if no launch has taken
+ *              it along yet and waits for all ranks; work enqueued on `stream` afterwards
+ *              sees d_all[r * cm_gather_stride(g) + b] = rank r's score b of that step
+ * Use one stream for all calls on a gather.  Every rank must make the same sequence of
+ * gathered launches (an empty slice is fine) and consume a step's buffer before the
+ * (depth-1)-th following gathered launch.  min_score must not be NaN.
+ * CM_GATHER_DEFER_WAIT skips the wait for the peers inside the ship (cm_gather_wait still
+ * performs it) and cm_gather_flush ships without waiting: both exist for driving several
+ * ranks from ONE thread on ONE GPU (the single-GPU tests), where a kernel must never wait
+ * for one that has not been launched.  cm_gather_import_ptr links blocks inside a process. */
+#define CM_GATHER_DEFER_WAIT 0x2u
+int cm_gather_create(cm_gather **out, cm_engine *e, int rank, int world,
+                     int max_guesses_per_rank, int depth);
+int cm_gather_destroy(cm_gather *g);
+int cm_gather_export(cm_gather *g, void *handle64);
+int cm_gather_import(cm_gather *g, int peer_rank, const void *handle64);
+int cm_gather_import_ptr(cm_gather *g, int peer_rank, void *d_block);
+int cm_gather_block(cm_gather *g, void **d_block, int64_t *bytes);
+int cm_gather_stride(cm_gather *g);
+int cm_score_batch_gather(cm_engine *e, cm_gather *g,
+                          const int32_t *d_guess_idx, const int32_t *d_guess_len,
+                          int n_guesses, int n_slots,
+                          const int32_t *d_answer_slot, const uint8_t *d_exact,
+                          float min_score, float *d_scores, int32_t *d_centi,
+                          uint32_t flags, void *stream);
+int cm_gather_result(cm_gather *g, float **d_gathered);
+int cm_gather_flush(cm_gather *g, void *stream);
+int cm_gather_wait(cm_gather *g, float **d_gathered, void *stream);
+int cm_gather_status(cm_gather *g, int *timed_out_rank_plus_1);
 
 /* ---- scoring without any allocation ---------------------------------------------------- *
  * No counterpart in the reference.  For callers that must not allocate GPU memory: programs

@@ -215,6 +215,72 @@ def test_pipe_matches_host_entry_point(small_engine):
     pipe.close()
 
 
+def test_fused_gather_single_gpu_emulation(small_engine):
+    """cm_gather_*: W ranks emulated on ONE GPU, one after the other on one stream.  The waits
+    for the peers are deferred (CM_GATHER_DEFER_WAIT, cm_gather_flush) so no kernel ever waits
+    for one that has not been launched.  A step is shipped by the NEXT launch of its rank (or
+    by flush/wait): every rank must end up with every rank's slice, step after step, with
+    more steps than ring slots."""
+    import torch
+    from cassmantle_b200._lib import CM_GATHER_DEFER_WAIT
+    from cassmantle_b200.dist import ScoreGather, shard_bounds
+    dev = torch.device("cuda:0")
+    W, B, N = 3, 1000, 4
+    idx, ln, ans, slot, ex = synth.make_guess_batch(B, N, 50_000, 2, seed=31, ragged=True)
+    small_engine.set_answers(ans)
+    want, _ = small_engine.score_host(idx, ln, slot, ex, 0.01)
+    per = -(-B // W)
+    gs = [ScoreGather(small_engine, per, depth=2, rank=r, world=W) for r in range(W)]
+    for r in range(W):
+        for q in range(W):
+            if q != r:
+                gs[r].link_local(q, gs[q])
+    stream = torch.cuda.Stream(device=dev)
+    st = stream.cuda_stream
+    t = [torch.from_numpy(a).to(dev) for a in (idx, ln, slot, ex)]
+    local = torch.empty(B, dtype=torch.float32, device=dev)
+    for step in range(5):                      # more steps than ring slots: buffers are reused
+        for rep in range(1 + step % 2):            # odd steps: two launches, the first shipped by the second
+            for r in range(W):
+                lo, hi = shard_bounds(B, W, r)
+                gs[r].score(t[0][lo:].data_ptr(), t[1][lo:].data_ptr(), hi - lo, N, t[2][lo:].data_ptr(),
+                            t[3][lo:].data_ptr(), 0.01, local[lo:].data_ptr(), st, flags=CM_GATHER_DEFER_WAIT)
+        for r in range(W):
+            gs[r].flush(st)                    # every rank ships before anybody waits
+        for r in range(W):
+            ptr = gs[r].wait(st)
+            stream.synchronize()
+            got = gs[r].as_tensor(ptr).cpu().numpy()
+            for q in range(W):
+                lo, hi = shard_bounds(B, W, q)
+                assert np.array_equal(got[q, : hi - lo].view(np.uint32), want[lo:hi].view(np.uint32))
+            assert gs[r].timed_out() == 0
+    assert np.array_equal(local.cpu().numpy().view(np.uint32), want.view(np.uint32))
+    # an empty slice still publishes its step
+    gs2 = [ScoreGather(small_engine, 8, depth=2, rank=r, world=2) for r in range(2)]
+    gs2[0].link_local(1, gs2[1]); gs2[1].link_local(0, gs2[0])
+    gs2[0].score(t[0].data_ptr(), t[1].data_ptr(), 8, N, t[2].data_ptr(), t[3].data_ptr(), 0.01,
+                 local.data_ptr(), st, flags=CM_GATHER_DEFER_WAIT)
+    gs2[1].score(0, 0, 0, N, 0, 0, 0.01, 0, st, flags=CM_GATHER_DEFER_WAIT)
+    gs2[0].flush(st)
+    p = gs2[1].wait(st)
+    stream.synchronize()
+    assert np.array_equal(gs2[1].as_tensor(p).cpu().numpy()[0, :8].view(np.uint32), want[:8].view(np.uint32))
+    assert gs2[1].timed_out() == 0
+    # a world of one waits only for itself: the in-kernel wait is safe on a single stream
+    g1 = ScoreGather(small_engine, B, depth=2, rank=0, world=1)
+    for _ in range(7):                         # ships ride in the following launches
+        g1.score(t[0].data_ptr(), t[1].data_ptr(), B, N, t[2].data_ptr(), t[3].data_ptr(), 0.01,
+                 local.data_ptr(), st, flags=1)
+    p1 = g1.wait(st)                           # the last step is shipped by the wait itself
+    assert p1 == g1.result()
+    stream.synchronize()
+    assert np.array_equal(g1.as_tensor(p1).cpu().numpy()[0, :B].view(np.uint32), want.view(np.uint32))
+    assert g1.timed_out() == 0
+    for g in gs + gs2 + [g1]:
+        g.close()
+
+
 # ---------------------------------------------------------------------------------------
 # edge cases the reference's semantics define
 # ---------------------------------------------------------------------------------------

@@ -29,6 +29,13 @@ torch.cuda.set_stream(stream)
 st = stream.cuda_stream
 ms32 = ctypes.c_float(np.float32(0.01))
 fn = lib.cm_score_batch_device
+GATHER = int(os.environ.get('CM_PROBE_GATHER', '0'))
+if GATHER:
+    from cassmantle_b200.dist import ScoreGather
+    gat = ScoreGather(eng, 65536, depth=4, rank=0, world=1)
+    fg = lib.cm_score_batch_gather
+    def fn(h, a, b, B, N, c, d, ms, o, ce, fl, st):
+        return fg(h, gat._h, a, b, B, N, c, d, ms, o, ce, fl, st)
 for B, N in shapes:
     ring = 8 if B * N > 1_000_000 else 64
     bufs = []
