@@ -268,7 +268,7 @@ def run_own(args) -> None:
     gather = None
     if world > 1 and args.collective == "fused":
         from cassmantle_b200.dist import ScoreGather
-        gather = ScoreGather(eng, B, depth=4)
+        gather = ScoreGather(eng, B, depth=8)
         gather.exchange_handles()
         dist.barrier()
 
@@ -347,6 +347,15 @@ def run_own(args) -> None:
             idx_r, ln_r, slot_r, ex_r = ring_r[last]
             want_r, _ = eng.score_host(idx_r, ln_r, slot_r, ex_r, MIN_SCORE)
             ok = ok and bool(np.array_equal(got[r, :B].view(np.uint32), want_r.view(np.uint32)))
+        if os.environ.get("CM_GATHER_TRACE") and rank == 0:
+            tr = np.zeros(512, dtype=np.uint64)
+            lib.cm_gather_trace(gather._h, tr.ctypes.data)
+            tr = tr.reshape(64, 8)
+            tr = tr[np.argsort(tr[:, 0])]
+            for row in tr[-12:]:
+                b0 = int(row[1])
+                print("trace step", int(row[0]), "start", b0 % 10**9, "order", int(row[2]) - b0, "stores", int(row[3]) - b0,
+                      "fence", int(row[4]) - b0, "flags", int(row[5]) - b0, "peers", int(row[6]) - b0, file=sys.stderr)
         t_ok = torch.tensor([1.0 if ok else 0.0], device=dev)
         dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
         gather_check = bool(t_ok.item() == 1.0)

@@ -68,6 +68,7 @@ _SIGNATURES = {
     "cm_gather_result": (_c.c_int, [_P, _c.POINTER(_P)]),
     "cm_gather_flush": (_c.c_int, [_P, _P]),
     "cm_gather_wait": (_c.c_int, [_P, _c.POINTER(_P), _P]),
+    "cm_gather_trace": (_c.c_int, [_P, _P]),
     "cm_gather_status": (_c.c_int, [_P, _c.POINTER(_c.c_int)]),
     "cm_score_batch_noalloc": (_c.c_int, [_c.c_int, _P, _c.c_int64, _c.c_int, _P, _c.c_int, _P, _P,
                                           _c.c_int, _c.c_int, _P, _P, _c.c_float, _P, _P, _P]),

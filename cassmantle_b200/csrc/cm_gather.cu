@@ -20,8 +20,9 @@
 // So a stream of gathered steps costs ONE launch per step and the exchange never sits on the
 // critical path.  Ordering: launch k+1's scoring CTAs store only after griddepcontrol.wait,
 // i.e. after launch k has finished including its ship CTA, so a staging slot (ring of `depth`
-// >= 2) is reset before it is written again, and no rank runs more than one launch ahead of
-// the slowest peer (every launch ends with the wait for all ranks' flags of the step before).
+// >= 2) is reset before it is written again.  A ship waits for the peers with a lag of depth/2
+// steps (a wait for the very same step couples all ranks every launch: 25.5 us/step on 8 GPUs),
+// so ranks drift at most depth/2 steps apart and a receive slot is safe for depth/2 launches.
 //
 // Designs measured and dropped (2 B200, 4096x16, us per step; one GPU alone: 12.7):
 //   NCCL all_gather_into_tensor after every scoring launch                              30.3
@@ -38,6 +39,7 @@
 
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -48,7 +50,8 @@ struct cm_gather {
     cm_engine *engine = nullptr;
     int rank = 0, world = 0, stride = 0, depth = 0;
     unsigned char *block = nullptr;   // [depth][world][stride] f32 | stage [depth][stride] | flags | counter | err
-    size_t block_bytes = 0, off_stage = 0, off_flags = 0, off_counter = 0, off_err = 0;
+    size_t block_bytes = 0, off_stage = 0, off_flags = 0, off_counter = 0, off_err = 0, off_trace = 0;
+    bool trace = false;
     unsigned char *peer[cm::kMaxPeers] = {};    // mapped blocks of every rank (peer[rank] == block)
     bool ipc_opened[cm::kMaxPeers] = {};
     uint32_t step = 0;                          // last step launched (scored)
@@ -121,7 +124,9 @@ int cm_gather_create(cm_gather **out, cm_engine *e, int rank, int world, int max
     g->off_flags = g->off_stage + cm::align_up((size_t)depth * g->stride * sizeof(float), 256);
     g->off_counter = g->off_flags + 256;
     g->off_err = g->off_counter + 256;
-    g->block_bytes = g->off_err + 256;
+    g->off_trace = g->off_err + 256;
+    g->block_bytes = g->off_trace + 64 * 8 * sizeof(unsigned long long);
+    g->trace = getenv("CM_GATHER_TRACE") != nullptr;
     cm::DeviceGuard guard(e->device);
     cudaError_t err = cudaMalloc(&g->block, g->block_bytes);
     if (err == cudaSuccess) err = cudaMemset(g->block, 0, g->block_bytes);
@@ -192,13 +197,16 @@ static ShipArgs make_ship(const cm_gather *g, bool spin) {
     a.copy_to = g->copy_of_step;
     a.counter = (unsigned *)(g->block + g->off_counter);
     a.err = (int *)(g->block + g->off_err);
+    a.trace = g->trace ? (unsigned long long *)(g->block + g->off_trace) : nullptr;
     a.timeout_cycles = kTimeoutCycles;
     a.step = g->step;
     a.world = g->world;
     a.rank = g->rank;
     a.stride = g->stride;
     a.n = g->n_of_step;
-    a.spin = spin ? 1 : 0;
+    // lagged coupling: a rank may run depth/2 steps ahead of the slowest peer, not more, so a
+    // receive slot is never overwritten while its owner may still be reading it
+    a.spin = spin ? 1 + g->depth / 2 : 0;
     return a;
 }
 
@@ -285,5 +293,14 @@ int cm_gather_status(cm_gather *g, int *timed_out_rank_plus_1) {
 }
 
 int cm_gather_stride(cm_gather *g) { return g ? g->stride : 0; }
+
+// Developer aid (CM_GATHER_TRACE=1): the last 64 ship traces, 8 x u64 each:
+// step, start, order-wait done, stores issued, fence done, flags published, peer wait done (ns).
+int cm_gather_trace(cm_gather *g, unsigned long long *out512) {
+    if (g == nullptr || out512 == nullptr) return fail(CM_ERR_INVALID, "NULL argument");
+    cm::DeviceGuard guard(g->engine->device);
+    CM_CUDA(cudaMemcpy(out512, g->block + g->off_trace, 64 * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return CM_OK;
+}
 
 }  // extern "C"

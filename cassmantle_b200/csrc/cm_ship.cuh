@@ -18,10 +18,18 @@ struct ShipArgs {
     float *copy_to;               // optional: a caller buffer that also receives my scores
     unsigned *counter;            // CTA arrival counter (only touched when several CTAs ship)
     int *err;                     // 0, or who timed out
+    unsigned long long *trace;    // developer trace (CM_GATHER_TRACE=1): 8 timestamps per step, or NULL
     long long timeout_cycles;
     uint32_t step;
-    int world, rank, stride, n, spin;
+    int world, rank, stride, n;
+    int spin;                     // 0: do not wait for the peers; k > 0: wait until they have shipped step-(k-1)
 };
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 
 __host__ __device__ inline int ship_ctas(int n) { return n > 0 ? (n + kShipChunk - 1) / kShipChunk : 1; }
 
@@ -50,11 +58,14 @@ __device__ __forceinline__ void spin_on_flags(const uint32_t *flags, int world, 
 //     optionally into the caller's buffer, and reset the slot to the sentinel
 //  3. fence.sys; the last CTA publishes the step in my entry of every peer's flag array
 //  4. unless deferred, wait (bounded) until every rank's flag in MY array has reached the step
+//     minus a lag: ranks may drift a few steps apart (ring depth) but never further
 __device__ __forceinline__ void ship_duty(const ShipArgs &a, int cta, int n_ctas) {
     __shared__ int s_last;
     const int lo = cta * kShipChunk;
     const int hi = min(a.n, lo + kShipChunk);
     const long long t0 = clock64();
+    unsigned long long *tr = (a.trace != nullptr && cta == 0 && threadIdx.x == 0) ? a.trace + (a.step % 64u) * 8u : nullptr;
+    if (tr) { tr[0] = a.step; tr[1] = global_ns(); }
     // 0. ships run strictly in step order.  A ship CTA does not honour the grid dependency of
     //    its launch, so with short kernels the ship of step s+depth can be resident before step
     //    s has been shipped -- and both use the same staging slot.  My own entry of my flag
@@ -72,6 +83,7 @@ __device__ __forceinline__ void ship_duty(const ShipArgs &a, int cta, int n_ctas
         }
     }
     __syncthreads();
+    if (tr) tr[2] = global_ns();
     for (int i = lo + 4 * (int)threadIdx.x; i < hi; i += 4 * (int)blockDim.x) {
         for (;;) {
             uint4 v;
@@ -101,20 +113,27 @@ __device__ __forceinline__ void ship_duty(const ShipArgs &a, int cta, int n_ctas
             __nanosleep(100);
         }
     }
+    if (tr) tr[3] = global_ns();
     __threadfence_system();
     __syncthreads();
+    if (tr) tr[4] = global_ns();
     if (threadIdx.x == 0) {
         s_last = (n_ctas == 1) || (atomicAdd(a.counter, 1u) == (unsigned)n_ctas - 1u);
-        if (s_last) {
-            if (n_ctas > 1) *a.counter = 0u;
-            __threadfence_system();
-            for (int r = 0; r < a.world; ++r)
-                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(a.flag[r] + a.rank), "r"(a.step)
-                             : "memory");
-        }
+        if (s_last && n_ctas > 1) *a.counter = 0u;
     }
     __syncthreads();
-    if (s_last && a.spin) spin_on_flags(a.my_flags, a.world, a.step, a.timeout_cycles, a.err);
+    // one thread per peer publishes: eight release stores from one thread cost ~2 us EACH
+    // (each waits for the previous remote store), eight threads overlap them
+    if (s_last && (int)threadIdx.x < a.world) {
+        __threadfence_system();
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(a.flag[threadIdx.x] + a.rank), "r"(a.step)
+                     : "memory");
+    }
+    __syncthreads();
+    if (tr) tr[5] = global_ns();
+    if (s_last && a.spin > 0 && a.step >= (uint32_t)a.spin)
+        spin_on_flags(a.my_flags, a.world, a.step - (uint32_t)(a.spin - 1), a.timeout_cycles, a.err);
+    if (tr) tr[6] = global_ns();
 }
 
 }  // namespace cm

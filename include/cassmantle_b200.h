@@ -167,7 +167,8 @@ int cm_pipe_wait(cm_pipe *p, int slot);
  *              sees d_all[r * cm_gather_stride(g) + b] = rank r's score b of that step
  * Use one stream for all calls on a gather.  Every rank must make the same sequence of
  * gathered launches (an empty slice is fine) and consume a step's buffer before the
- * (depth-1)-th following gathered launch.  min_score must not be NaN.
+ * (depth/2)-th following gathered launch (ranks may drift depth/2 steps apart, not more).
+ * min_score must not be NaN.
  * CM_GATHER_DEFER_WAIT skips the wait for the peers inside the ship (cm_gather_wait still
  * performs it) and cm_gather_flush ships without waiting: both exist for driving several
  * ranks from ONE thread on ONE GPU (the single-GPU tests), where a kernel must never wait
@@ -191,6 +192,7 @@ int cm_gather_result(cm_gather *g, float **d_gathered);
 int cm_gather_flush(cm_gather *g, void *stream);
 int cm_gather_wait(cm_gather *g, float **d_gathered, void *stream);
 int cm_gather_status(cm_gather *g, int *timed_out_rank_plus_1);
+int cm_gather_trace(cm_gather *g, unsigned long long *out512);   /* developer aid, see cm_gather.cu */
 
 /* ---- scoring without any allocation ---------------------------------------------------- *
  * No counterpart in the reference.  For callers that must not allocate GPU memory: programs
