@@ -33,6 +33,7 @@ extern "C" {
 typedef struct cm_engine cm_engine;
 typedef struct cm_pipe cm_pipe;
 typedef struct cm_gather cm_gather;
+typedef struct cm_vocab cm_vocab;
 
 typedef enum cm_status {
     CM_OK = 0,
@@ -145,6 +146,34 @@ int cm_pipe_buffers(cm_pipe *p, int slot, int n_guesses, int n_slots,
                     uint8_t **exact, float **scores, int32_t **centi);
 int cm_pipe_submit(cm_pipe *p, int slot, float min_score, int want_centi);
 int cm_pipe_wait(cm_pipe *p, int slot);
+
+/* ---- vocabulary lookup on the device -------------------------------- *
+ * Replaces `inputs.lower()` (src/backend.py:304) + gensim's `key_to_index[word]` dict lookup
+ * inside `wv.similarity` (src/backend.py:307): an open-addressing hash table in HBM, built
+ * once from the keys in index_to_key order (key i -> row i; the first occurrence of a
+ * duplicate key wins, as in a dict).  Keys are UTF-8 bytes, `keys + key_offsets[i]` ..
+ * `keys + key_offsets[i+1]`.  A query word is lower-cased (ASCII A-Z only; lower other text
+ * first, as Python would) and looked up: its row, or -1 where the reference raises KeyError.
+ * Integer work: results are bit-exact against the Python dict.                             */
+int cm_vocab_create(cm_vocab **out, cm_engine *e, const char *keys, const int64_t *key_offsets,
+                    int64_t n_keys);
+int cm_vocab_destroy(cm_vocab *v);
+int cm_vocab_size(cm_vocab *v, int64_t *n_keys, int64_t *n_slots);
+/* words i = bytes[offsets[i] .. offsets[i+1]), i < n_words; rows[i] = table row or -1.       */
+int cm_vocab_lookup_device(cm_vocab *v, const uint8_t *d_bytes, const int32_t *d_offsets,
+                           int n_words, int32_t *d_rows, void *stream);
+int cm_vocab_lookup_host(cm_vocab *v, const uint8_t *bytes, const int32_t *offsets,
+                         int n_words, int32_t *rows);
+/* Backend.compute_scores (src/backend.py:312-317) for one-word guesses with the STRINGS
+ * handed to the device: lower(), string equality with the answer (-> 1.0), key lookup of
+ * guesses and answers (unknown -> min_score), similarity, floor.  guess i is
+ * guess_bytes[guess_offsets[i] .. guess_offsets[i+1]) and is scored against answer
+ * answer_slot[i] of the n_answers answer strings.  Blocking; re-registers the engine's
+ * answers (as cm_set_answers would).                                                        */
+int cm_score_words_host(cm_engine *e, cm_vocab *v,
+                        const uint8_t *guess_bytes, const int32_t *guess_offsets, int n_guesses,
+                        const uint8_t *answer_bytes, const int32_t *answer_offsets, int n_answers,
+                        const int32_t *answer_slot, float min_score, float *scores, int32_t *centi);
 
 /* ---- several GPUs: score all-gather over NVLink peer memory ---------------------------- *
  * No reference counterpart (the reference has no collective).  SURVEY.md §8e: one process

@@ -252,3 +252,15 @@ def pairs_to_batch(key_to_index: Dict[str, int], data: Dict[str, Dict[str, str]]
         g[n, 0] = key_to_index.get(i, -1)
         a[n] = key_to_index.get(w, -1)
     return keys, g, np.ones(len(keys), dtype=np.int32), a, np.arange(len(keys), dtype=np.int32), ex
+
+
+# --------------------------------------------------------------------------- #
+# Vocabulary lookup: the reference's mechanism IS a Python dict.
+# --------------------------------------------------------------------------- #
+def lookup_rows(index_to_key: Sequence[str], words: Sequence[str]) -> np.ndarray:
+    """``key_to_index.get(word.lower(), -1)`` with gensim's first-occurrence-wins dict
+    (src/backend.py:304 + the lookup inside wv.similarity at src/backend.py:307)."""
+    k2i: Dict[str, int] = {}
+    for i, k in enumerate(index_to_key):
+        k2i.setdefault(k, i)
+    return np.asarray([k2i.get(w.lower(), -1) for w in words], dtype=np.int32)

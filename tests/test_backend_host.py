@@ -82,3 +82,17 @@ def test_empty_payload(golden):
     be, _, eng = _pair(golden)
     assert asyncio.run(be.compute_scores({})) == {}
     assert eng.calls == 0
+
+
+def test_pack_words_format():
+    from cassmantle_b200.vocab import pack_words
+    data, off = pack_words(["ab", "", "CÉ", "d"])
+    assert off.tolist() == [0, 2, 2, 5, 6] and off.dtype == np.int32
+    assert bytes(data[:6]) == "abcéd".encode()            # non-ASCII text is lowered on the host
+    data, off = pack_words([])
+    assert off.tolist() == [0]
+
+
+def test_lookup_oracle_first_occurrence_wins():
+    rows = O.lookup_rows(["a", "B", "a", "b"], ["A", "b", "B", "c", ""])
+    assert rows.tolist() == [0, 3, 3, -1, -1]
