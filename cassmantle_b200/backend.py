@@ -107,5 +107,16 @@ class Backend:
             scores.update({key: str(score)})                          # backend.py:316
         return scores
 
+    def most_similar(self, word: str, topn: int = 50) -> List[Tuple[str, float]]:
+        """src/backend.py:297-301: ``self.wv.most_similar(word.lower(), topn=topn)``."""
+        try:
+            row = self.vocab.key_to_index[word.lower()]
+        except KeyError as e:
+            raise Exception("Word not in dictionary. ", e)
+        rows, sims = self.engine.most_similar(row, topn + 1)      # gensim: topn + len(all_keys)
+        keys = self.vocab.index_to_key
+        result = [(keys[int(r)], float(s)) for r, s in zip(rows, sims) if int(r) != row]
+        return result[:topn]
+
     def score_to_blur(self, score: float, min_blur: float = 0.0, max_blur: float = 15):
         return min_blur + (1 - score ** 2) * (max_blur - min_blur)    # backend.py:319-320

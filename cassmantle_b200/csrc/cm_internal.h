@@ -8,6 +8,8 @@
 #include "../../include/cassmantle_b200.h"
 #include "cm_ship.cuh"
 
+struct cm_similar_state;   // scratch of cm_most_similar (cm_similar.cu), allocated on first use
+
 struct cm_engine {
     int device = 0;
     int64_t n_rows = 0;
@@ -20,6 +22,7 @@ struct cm_engine {
     // pinned staging for the host-buffer entry point when the caller's memory is pageable
     unsigned char *h_stage = nullptr;
     size_t stage_bytes = 0;
+    cm_similar_state *similar = nullptr;
     std::mutex mu;
 };
 
@@ -55,6 +58,9 @@ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 bool is_pinned_host(const void *p);
 
 int check_engine(const cm_engine *e);
+
+void similar_state_free(cm_engine *e);     // cm_similar.cu
+void similar_invalidate(cm_engine *e);     // the table changed: cached row norms are stale
 
 // Validates the arguments and enqueues the scoring kernel; pointers may be device memory or
 // pinned host memory (the kernel then reads / writes it across PCIe itself).  `ship`, if not

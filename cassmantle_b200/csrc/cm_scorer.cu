@@ -553,6 +553,7 @@ int cm_engine_destroy(cm_engine *e) {
     {
         DeviceGuard guard(e->device);
         if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
+        cm::similar_state_free(e);
         if (e->d_table) cudaFree(e->d_table);
         if (e->d_ans_unit) cudaFree(e->d_ans_unit);
         if (e->d_ans_rows) cudaFree(e->d_ans_rows);
@@ -572,6 +573,7 @@ int cm_engine_upload_rows(cm_engine *e, const float *rows, int64_t row0, int64_t
     CM_CUDA(cudaMemcpyAsync(e->d_table + (size_t)row0 * e->dim, rows,
                             (size_t)n * e->dim * sizeof(float), cudaMemcpyHostToDevice, e->stream));
     CM_CUDA(cudaStreamSynchronize(e->stream));
+    cm::similar_invalidate(e);
     return CM_OK;
 }
 
@@ -597,6 +599,7 @@ int cm_engine_fill_synthetic(cm_engine *e, uint32_t seed) {
     cm::count_launch();
     CM_CUDA(cudaGetLastError());
     CM_CUDA(cudaStreamSynchronize(e->stream));
+    cm::similar_invalidate(e);
     return CM_OK;
 }
 

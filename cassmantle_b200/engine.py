@@ -128,6 +128,15 @@ class ScoringEngine:
                 ctypes.c_float(np.float32(min_score)), scores.ctypes.data, _ptr(centi)))
         return scores, centi
 
+    def most_similar(self, row: int, k: int) -> Tuple[np.ndarray, np.ndarray]:
+        """The k rows with the highest cosine to ``row`` (itself included), best first."""
+        rows = np.empty(k, dtype=np.int32)
+        sims = np.empty(k, dtype=np.float32)
+        n = ctypes.c_int(0)
+        check(self._lib.cm_most_similar(self._h, int(row), int(k), rows.ctypes.data, sims.ctypes.data,
+                                        ctypes.byref(n)))
+        return rows[: n.value], sims[: n.value]
+
     def score_device(self, d_guess_idx: int, d_guess_len: int, n_guesses: int, n_slots: int,
                      d_answer_slot: int, d_exact: int, min_score: float, d_scores: int,
                      d_centi: int = 0, stream: Optional[int] = None, flags: int = 0) -> None:

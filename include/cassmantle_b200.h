@@ -175,6 +175,16 @@ int cm_score_words_host(cm_engine *e, cm_vocab *v,
                         const uint8_t *answer_bytes, const int32_t *answer_offsets, int n_answers,
                         const int32_t *answer_slot, float min_score, float *scores, int32_t *centi);
 
+/* ---- most_similar ------------------------------------------------- *
+ * Backend.most_similar, src/backend.py:297-301 = gensim KeyedVectors.most_similar(
+ * positive=[word], topn): cosine of the word's row against EVERY row (one pass over the
+ * table), then the k best.  `row` is the word's table row (the caller raises for unknown
+ * words, as the reference does); rows_out/sims_out receive the k best rows by descending
+ * cosine INCLUDING `row` itself -- gensim asks for topn+1 and drops the query, so pass
+ * k = topn + 1 and drop it too.  k <= 1024.  Blocking; the first call also computes the row
+ * norms (gensim's fill_norms).  NaN cosines rank last.                                       */
+int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_out, float *sims_out, int *n_out);
+
 /* ---- several GPUs: score all-gather over NVLink peer memory ---------------------------- *
  * No reference counterpart (the reference has no collective).  SURVEY.md §8e: one process
  * per GPU, a table replica each, every rank scores its slice of the batch and every rank

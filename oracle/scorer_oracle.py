@@ -264,3 +264,28 @@ def lookup_rows(index_to_key: Sequence[str], words: Sequence[str]) -> np.ndarray
     for i, k in enumerate(index_to_key):
         k2i.setdefault(k, i)
     return np.asarray([k2i.get(w.lower(), -1) for w in words], dtype=np.int32)
+
+
+# --------------------------------------------------------------------------- #
+# most_similar: src/backend.py:297-301 -> gensim KeyedVectors.most_similar
+# --------------------------------------------------------------------------- #
+def most_similar_dists(table: np.ndarray, row: int) -> np.ndarray:
+    """gensim 4.x, positive=[word]: dists = dot(vectors, mean) / norms with
+    norms = np.linalg.norm(vectors, axis=1) and mean = unitvec(vectors[row] / norms[row])."""
+    norms = np.linalg.norm(table, axis=1)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        mean = unitvec(np.array([table[row] / norms[row]]).mean(axis=0)).astype(np.float32)
+        return np.dot(table, mean) / norms
+
+
+def most_similar_rows(table: np.ndarray, row: int, topn: int = 50):
+    """[(row, float(sim))] best first, the query row dropped (gensim asks for topn + 1)."""
+    dists = most_similar_dists(table, row)
+    x = -dists                                              # matutils.argsort(..., reverse=True)
+    k = topn + 1
+    if k >= x.size:
+        best = np.argsort(x)[:k]
+    else:
+        part = np.argpartition(x, k)[:k]
+        best = part.take(np.argsort(x.take(part)))
+    return [(int(r), float(dists[r])) for r in best if int(r) != row][:topn]
