@@ -1,0 +1,296 @@
+// cassmantle_b200 -- per-session image blur on the device (include/...: cm_blur_*).
+//
+// SURVEY.md §8f rank 3.  Reference: Backend.score_to_blur + Backend.mask_image,
+// src/backend.py:319-324, called per request from Server.fetch_masked_image
+// (src/server.py:129-133):
+//     blur  = min_blur + (1 - score**2) * (max_blur - min_blur)
+//     image.filter(ImageFilter.GaussianBlur(blur))
+// Pillow's GaussianBlur is NOT a Gaussian convolution: it is three passes of an "extended box
+// blur" per axis (libImaging/BoxBlur.c), all in 32-bit integer arithmetic with a rounding to
+// uint8 after every pass.  This file restates that arithmetic so the result is bit-identical:
+//
+//   box radius  r' = l + a   from sigma^2 = radius^2 / 3 (Gwosdek et al., float32 as in Pillow)
+//   one pass    out[x] = (acc*ww + (in[x-r-1] + in[x+r+1])*fw + 2^23) >> 24      (uint32 wrap)
+//               acc = sum of in[clamp(i)] for i in [x-r, x+r], r = int(r'),
+//               ww = (uint32)(2^24 / (2 r' + 1)),  fw = (2^24 - (2r+1) ww) / 2
+//   image       3 passes along x, then 3 passes along y (Pillow transposes, blurs along x
+//               again and transposes back -- the same thing)
+//
+// The running accumulator of the C code becomes a per-line prefix sum in shared memory (exact:
+// it is an integer sum), so every output pixel of a line is computed independently.  One CTA
+// per (line, request); the same source image serves a whole batch of sessions, each with its
+// own radius -- that is the batch dimension of this path.
+
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstring>
+#include <new>
+#include <vector>
+
+#include "cm_internal.h"
+
+struct cm_blur {
+    int device = 0;
+    int max_h = 0, max_w = 0, channels = 0, max_batch = 0;
+    int h = 0, w = 0;                 // current image
+    uint8_t *d_src = nullptr;         // the round's image
+    uint8_t *d_a = nullptr;           // ping  [max_batch][h*w*c]
+    uint8_t *d_b = nullptr;           // pong
+    uint8_t *h_pin = nullptr;         // pinned staging for results
+    void *d_params = nullptr;         // BoxParams[max_batch]
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+};
+
+namespace {
+
+using cm::fail;
+
+struct BoxParams {
+    int radius;         // int(r')
+    uint32_t ww, fw;
+    int identity;       // GaussianBlur(0) returns a copy
+};
+
+// Pillow _gaussian_blur_radius + ImagingHorizontalBoxBlur's weights, float32 step by step.
+BoxParams box_params(float gaussian_radius) {
+    BoxParams p = {0, 1u << 24, 0u, 0};
+    if (gaussian_radius == 0.0f) { p.identity = 1; return p; }
+    volatile float sigma2 = gaussian_radius * gaussian_radius / 3.0f;
+    volatile float L = (float)std::sqrt(12.0 * (double)sigma2 + 1.0);
+    volatile float l = (float)std::floor(((double)L - 1.0) / 2.0);
+    volatile float t1 = 2.0f * l + 1.0f;
+    volatile float t2 = l * (l + 1.0f);
+    volatile float t3 = 3.0f * sigma2;
+    volatile float t4 = t2 - t3;
+    volatile float a = t1 * t4;
+    volatile float lp1 = l + 1.0f;
+    volatile float t5 = lp1 * lp1;
+    volatile float t6 = sigma2 - t5;
+    volatile float t7 = 6.0f * t6;
+    a = a / t7;
+    volatile float fr = l + a;
+    p.radius = (int)fr;
+    volatile float denom = fr * 2.0f + 1.0f;
+    volatile float q = (float)(1u << 24) / denom;
+    p.ww = (uint32_t)q;
+    p.fw = ((1u << 24) - (uint32_t)(p.radius * 2 + 1) * p.ww) / 2u;
+    return p;
+}
+
+// One box-blur pass along a "line" of `n` pixels of C channels.  Pixel x of line `line` of request
+// `b` lives at  base + b*req_stride + line*line_stride + x*pix_stride  (bytes).
+template <int C>
+__global__ void __launch_bounds__(256)
+cm_boxblur_kernel(const uint8_t *__restrict__ src, size_t src_req_stride, uint8_t *__restrict__ dst,
+                  size_t dst_req_stride, int n, size_t line_stride, size_t pix_stride,
+                  const BoxParams *__restrict__ params) {
+    extern __shared__ uint32_t smem[];
+    uint32_t *P = smem;                                   // [C][n + 1] exclusive prefix sums
+    uint8_t *px = reinterpret_cast<uint8_t *>(smem + (size_t)C * (n + 1));   // [n][C] the line itself
+    __shared__ uint32_t warp_tot[8][C];
+    const BoxParams bp = params[blockIdx.y];
+    const uint8_t *in = src + blockIdx.y * src_req_stride + blockIdx.x * line_stride;
+    uint8_t *out = dst + blockIdx.y * dst_req_stride + blockIdx.x * line_stride;
+    const int t = threadIdx.x;
+
+    for (int x = t; x < n; x += 256) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) px[x * C + c] = in[x * pix_stride + c];
+    }
+    __syncthreads();
+    if (bp.identity) {
+        for (int x = t; x < n; x += 256) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) out[x * pix_stride + c] = px[x * C + c];
+        }
+        return;
+    }
+    // block-wide exclusive scan: thread t owns pixels [t*chunk, (t+1)*chunk)
+    const int chunk = (n + 255) / 256;
+    const int x0 = min(t * chunk, n), x1 = min(x0 + chunk, n);
+    uint32_t local[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) local[c] = 0;
+    for (int x = x0; x < x1; ++x) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) local[c] += px[x * C + c];
+    }
+    uint32_t incl[C];
+    const int lane = t & 31, wid = t >> 5;
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        uint32_t v = local[c];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t u = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += u;
+        }
+        incl[c] = v;
+        if (lane == 31) warp_tot[wid][c] = v;
+    }
+    __syncthreads();
+    uint32_t run[C];
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        uint32_t base = 0;
+        for (int w = 0; w < wid; ++w) base += warp_tot[w][c];
+        run[c] = base + incl[c] - local[c];               // exclusive prefix at x0
+    }
+    for (int x = x0; x < x1; ++x) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            P[c * (n + 1) + x] = run[c];
+            run[c] += px[x * C + c];
+        }
+    }
+    if (x1 == n && x0 < n) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) P[c * (n + 1) + n] = run[c];
+    }
+    if (n == 0) return;
+    __syncthreads();
+    const int r = bp.radius, last = n - 1;
+    for (int x = t; x < n; x += 256) {
+        const int hi = min(x + r, last), lo = max(x - r, 0);
+        const uint32_t n_left = (uint32_t)max(r - x, 0), n_right = (uint32_t)max(x + r - last, 0);
+        const int far_l = max(x - r - 1, 0), far_r = min(x + r + 1, last);
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            const uint32_t acc = P[c * (n + 1) + hi + 1] - P[c * (n + 1) + lo] + n_left * px[c] +
+                                 n_right * px[last * C + c];
+            const uint32_t bulk = acc * bp.ww + ((uint32_t)px[far_l * C + c] + (uint32_t)px[far_r * C + c]) * bp.fw;
+            out[x * pix_stride + c] = (uint8_t)((bulk + (1u << 23)) >> 24);
+        }
+    }
+}
+
+template <int C>
+int launch_pass(cm_blur *b, const uint8_t *src, size_t src_req_stride, uint8_t *dst, size_t dst_req_stride,
+                int n_lines, int n, size_t line_stride, size_t pix_stride, int batch) {
+    const size_t smem = (size_t)C * (n + 1) * sizeof(uint32_t) + (size_t)n * C;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(cm_boxblur_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        attr_set = true;
+    }
+    cm_boxblur_kernel<C><<<dim3((unsigned)n_lines, (unsigned)batch), 256, smem, b->stream>>>(
+        src, src_req_stride, dst, dst_req_stride, n, line_stride, pix_stride, (const BoxParams *)b->d_params);
+    cm::count_launch();
+    CM_CUDA(cudaGetLastError());
+    return CM_OK;
+}
+
+template <int C>
+int blur_batch(cm_blur *b, int batch, uint8_t **result) {
+    const size_t img = (size_t)b->h * b->w * C;
+    const size_t row = (size_t)b->w * C;
+    // along x: lines are rows
+    if (int rc = launch_pass<C>(b, b->d_src, 0, b->d_a, img, b->h, b->w, row, C, batch)) return rc;
+    if (int rc = launch_pass<C>(b, b->d_a, img, b->d_b, img, b->h, b->w, row, C, batch)) return rc;
+    if (int rc = launch_pass<C>(b, b->d_b, img, b->d_a, img, b->h, b->w, row, C, batch)) return rc;
+    // along y: lines are columns
+    if (int rc = launch_pass<C>(b, b->d_a, img, b->d_b, img, b->w, b->h, C, row, batch)) return rc;
+    if (int rc = launch_pass<C>(b, b->d_b, img, b->d_a, img, b->w, b->h, C, row, batch)) return rc;
+    if (int rc = launch_pass<C>(b, b->d_a, img, b->d_b, img, b->w, b->h, C, row, batch)) return rc;
+    *result = b->d_b;
+    return CM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int cm_blur_destroy(cm_blur *b) {
+    if (b == nullptr) return CM_OK;
+    {
+        cm::DeviceGuard guard(b->device);
+        if (b->stream) { cudaStreamSynchronize(b->stream); cudaStreamDestroy(b->stream); }
+        if (b->d_src) cudaFree(b->d_src);
+        if (b->d_a) cudaFree(b->d_a);
+        if (b->d_b) cudaFree(b->d_b);
+        if (b->d_params) cudaFree(b->d_params);
+        if (b->h_pin) cudaFreeHost(b->h_pin);
+    }
+    delete b;
+    return CM_OK;
+}
+
+int cm_blur_create(cm_blur **out, int device, int max_height, int max_width, int channels, int max_batch) {
+    if (out == nullptr) return fail(CM_ERR_INVALID, "out is NULL");
+    *out = nullptr;
+    if (max_height < 1 || max_width < 1 || max_height > 8192 || max_width > 8192)
+        return fail(CM_ERR_INVALID, "image size %dx%d outside [1, 8192]", max_width, max_height);
+    if (channels != 1 && channels != 3 && channels != 4)
+        return fail(CM_ERR_INVALID, "channels %d must be 1 (L), 3 (RGB) or 4 (RGBA)", channels);
+    if (max_batch < 1 || max_batch > 1024) return fail(CM_ERR_INVALID, "max_batch %d outside [1, 1024]", max_batch);
+    int n_dev = 0;
+    CM_CUDA(cudaGetDeviceCount(&n_dev));
+    if (device < 0 || device >= n_dev) return fail(CM_ERR_INVALID, "device %d not in [0, %d)", device, n_dev);
+    cm_blur *b = new (std::nothrow) cm_blur();
+    if (b == nullptr) return fail(CM_ERR_NOMEM, "blur allocation failed");
+    b->device = device; b->max_h = max_height; b->max_w = max_width; b->channels = channels; b->max_batch = max_batch;
+    const size_t img = (size_t)max_height * max_width * channels;
+    cm::DeviceGuard guard(device);
+    cudaError_t err = cudaMalloc(&b->d_src, img);
+    if (err == cudaSuccess) err = cudaMalloc(&b->d_a, img * max_batch);
+    if (err == cudaSuccess) err = cudaMalloc(&b->d_b, img * max_batch);
+    if (err == cudaSuccess) err = cudaMalloc(&b->d_params, sizeof(BoxParams) * max_batch);
+    if (err == cudaSuccess) err = cudaHostAlloc(&b->h_pin, img * max_batch, cudaHostAllocDefault);
+    if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking);
+    if (err != cudaSuccess) {
+        cudaGetLastError();
+        const int code = fail(CM_ERR_NOMEM, "blur buffers (%zu bytes x %d) failed: %s", img, 2 * max_batch + 1,
+                              cudaGetErrorString(err));
+        cm_blur_destroy(b);
+        return code;
+    }
+    *out = b;
+    return CM_OK;
+}
+
+int cm_blur_set_image(cm_blur *b, const uint8_t *pixels, int height, int width) {
+    if (b == nullptr || pixels == nullptr) return fail(CM_ERR_INVALID, "NULL argument");
+    if (height < 1 || width < 1 || height > b->max_h || width > b->max_w)
+        return fail(CM_ERR_INVALID, "image %dx%d exceeds the %dx%d this object was created for", width, height,
+                    b->max_w, b->max_h);
+    std::lock_guard<std::mutex> lock(b->mu);
+    cm::DeviceGuard guard(b->device);
+    CM_CUDA(cudaMemcpyAsync(b->d_src, pixels, (size_t)height * width * b->channels, cudaMemcpyHostToDevice, b->stream));
+    CM_CUDA(cudaStreamSynchronize(b->stream));
+    b->h = height; b->w = width;
+    return CM_OK;
+}
+
+int cm_blur_batch_host(cm_blur *b, const float *radii, int n, uint8_t *out) {
+    if (b == nullptr) return fail(CM_ERR_INVALID, "blur is NULL");
+    if (n < 0 || n > b->max_batch) return fail(CM_ERR_INVALID, "n %d outside [0, %d]", n, b->max_batch);
+    if (n == 0) return CM_OK;
+    if (radii == nullptr || out == nullptr) return fail(CM_ERR_INVALID, "radii or out is NULL");
+    if (b->h == 0) return fail(CM_ERR_STATE, "cm_blur_set_image has not been called");
+    std::vector<BoxParams> params((size_t)n);
+    for (int i = 0; i < n; ++i) {
+        if (!(radii[i] >= 0.0f) || radii[i] > 4096.0f)
+            return fail(CM_ERR_INVALID, "radius %g of request %d outside [0, 4096]", (double)radii[i], i);
+        params[(size_t)i] = box_params(radii[i]);
+    }
+    std::lock_guard<std::mutex> lock(b->mu);
+    cm::DeviceGuard guard(b->device);
+    CM_CUDA(cudaMemcpyAsync(b->d_params, params.data(), sizeof(BoxParams) * n, cudaMemcpyHostToDevice, b->stream));
+    uint8_t *result = nullptr;
+    int rc;
+    switch (b->channels) {
+        case 1: rc = blur_batch<1>(b, n, &result); break;
+        case 3: rc = blur_batch<3>(b, n, &result); break;
+        default: rc = blur_batch<4>(b, n, &result); break;
+    }
+    if (rc != CM_OK) return rc;
+    const size_t bytes = (size_t)b->h * b->w * b->channels * n;
+    CM_CUDA(cudaMemcpyAsync(b->h_pin, result, bytes, cudaMemcpyDeviceToHost, b->stream));
+    CM_CUDA(cudaStreamSynchronize(b->stream));
+    memcpy(out, b->h_pin, bytes);
+    return CM_OK;
+}
+
+}  // extern "C"

@@ -34,6 +34,7 @@ typedef struct cm_engine cm_engine;
 typedef struct cm_pipe cm_pipe;
 typedef struct cm_gather cm_gather;
 typedef struct cm_vocab cm_vocab;
+typedef struct cm_blur cm_blur;
 
 typedef enum cm_status {
     CM_OK = 0,
@@ -184,6 +185,23 @@ int cm_score_words_host(cm_engine *e, cm_vocab *v,
  * k = topn + 1 and drop it too.  k <= 1024.  Blocking; the first call also computes the row
  * norms (gensim's fill_norms).  NaN cosines rank last.                                       */
 int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_out, float *sims_out, int *n_out);
+
+/* ---- per-session image blur ---------------------------------------- *
+ * Backend.mask_image, src/backend.py:322-324: image.filter(ImageFilter.GaussianBlur(blur))
+ * with blur = score_to_blur(score) (src/backend.py:319-320), run per request by
+ * Server.fetch_masked_image (src/server.py:129-133).  Pillow's GaussianBlur is three passes
+ * per axis of an extended box blur in 32-bit integer arithmetic; this restates it exactly,
+ * so the output bytes are identical to Pillow's.  The round's image is uploaded once
+ * (cm_blur_set_image: interleaved uint8, height x width x channels, channels 1/3/4 =
+ * Pillow modes L/RGB/RGBA); cm_blur_batch_host blurs it for n sessions at once, request i
+ * with Gaussian radius radii[i] (the caller evaluates score_to_blur exactly as the reference
+ * does and passes it as a float, which is what Pillow's C entry point receives), and
+ * returns n images back to back in `out`.  Blocking.                                       */
+int cm_blur_create(cm_blur **out, int device, int max_height, int max_width, int channels,
+                   int max_batch);
+int cm_blur_destroy(cm_blur *b);
+int cm_blur_set_image(cm_blur *b, const uint8_t *pixels, int height, int width);
+int cm_blur_batch_host(cm_blur *b, const float *radii, int n, uint8_t *out);
 
 /* ---- several GPUs: score all-gather over NVLink peer memory ---------------------------- *
  * No reference counterpart (the reference has no collective).  SURVEY.md §8e: one process
