@@ -504,7 +504,7 @@ def run_own(args) -> None:
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of cm_score_kernel at 4096x16 from the
 # committed `ncu --set full` capture (profiles/).
-TRAFFIC_BYTES_PER_LAUNCH = 81_421_568   # profiles/r1_v2_4096x16.summary.txt (79.75 MB read + 1.67 MB written)
+TRAFFIC_BYTES_PER_LAUNCH = 81_531_648   # profiles/r1_v3_4096x16.summary.txt (79.76 MB read + 1.77 MB written)
 
 
 def main() -> None:
