@@ -450,6 +450,42 @@ def run_own(args) -> None:
         assert np.array_equal(h_scores_np.view(np.uint32),
                               np.asarray(views[j]["scores"]).view(np.uint32)) or args.steps < RING
 
+    # ---- the other BASELINE.json shapes, kernel only (N = 1 is the only shape
+    #      the reference itself produces; the seq-N shapes are the labelled mean-pool extension)
+    other = None
+    if rank == 0 and world == 1 and not args.no_other_shapes:
+        other = []
+        for (b2, n2, tag) in [(4096, 1, "reference shape, one word per guess"),
+                              (65536, 1, "configs[3] at one word per guess"),
+                              (512, 8, "configs[1] micro-batch"),
+                              (65536, 16, "configs[3] scale-out batch on one GPU"),
+                              (16384, 64, "configs[4] long-guess stress")]:
+            k_ring = 8
+            bufs = []
+            for i in range(k_ring):
+                idx2, ln2, _, slot2, ex2 = synth.make_guess_batch(b2, n2, V, N_ANSWERS, seed=7000 + i, near_frac=0.0)
+                bufs.append([torch.from_numpy(a).to(dev) for a in (idx2, ln2, slot2, ex2)])
+            out2 = torch.empty(b2, dtype=torch.float32, device=dev)
+            ptr2 = [(q[0].data_ptr(), q[1].data_ptr(), q[2].data_ptr(), q[3].data_ptr()) for q in bufs]
+            reps = 300 if b2 * n2 < 500_000 else 60
+            for i in range(10):
+                q = ptr2[i % k_ring]
+                fn(h, q[0], q[1], b2, n2, q[2], q[3], ms32, out2.data_ptr(), None, OVERLAP, st)
+            torch.cuda.synchronize()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record(stream)
+            for i in range(reps):
+                q = ptr2[i % k_ring]
+                fn(h, q[0], q[1], b2, n2, q[2], q[3], ms32, out2.data_ptr(), None, OVERLAP, st)
+            s1.record(stream)
+            torch.cuda.synchronize()
+            us2 = s0.elapsed_time(s1) * 1e3 / reps
+            alg = b2 * (n2 * (D * 4 + 4) + 8)
+            other.append({"guesses": b2, "word_slots": n2, "note": tag, "kernel_us": us2,
+                          "guesses_per_s": b2 / (us2 * 1e-6), "achieved_gbs": alg / (us2 * 1e-6) / 1e9,
+                          "frac_of_hbm_peak": alg / (us2 * 1e-6) / 1e9 / peak})
+            del bufs, out2
+
     # ---- single-call latency on the micro-batch shape (configs[1]: 512 guesses x 8) ------
     lat = None
     if rank == 0:
@@ -492,6 +528,7 @@ def run_own(args) -> None:
                        "l2": f"ring of {RING} distinct batches over a 3.6 GB table (inputs >> L2)"},
             "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
             "cpu_baseline": cpu_baseline, "clocks": clocks, "latency": lat, "parity": parity,
+            "other_shapes": other,
         }
         print(json.dumps(line), flush=True)
     if gather is not None:
@@ -519,6 +556,7 @@ def main() -> None:
     ap.add_argument("--roofline-s", type=float, default=1.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"])
+    ap.add_argument("--no-other-shapes", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
