@@ -226,6 +226,15 @@ def run_own(args) -> None:
             t1 = time.perf_counter()
             _cpu_worker((2, 0, 2048))
             single = 2048 / (time.perf_counter() - t1)
+        # the "strong" CPU baseline of BASELINE.md: same math, compiled C, one pthread per core
+        from oracle import c_oracle
+        idx0, ln0, slot0, ex0 = ring[0]
+        c_oracle.score_batch(_CPU["table"], idx0, ln0, ans, slot0, ex0, MIN_SCORE, threads=workers)
+        t2 = time.perf_counter()
+        for i in range(1, 9):
+            idx_i, ln_i, slot_i, ex_i = ring[i]
+            c_oracle.score_batch(_CPU["table"], idx_i, ln_i, ans, slot_i, ex_i, MIN_SCORE, threads=workers)
+        c_port = 8 * B / (time.perf_counter() - t2)
         cpu.close()
         cpu_check = outs
         cpu_baseline = {
@@ -234,6 +243,7 @@ def run_own(args) -> None:
                       f"Python loop = oracle port of src/backend.py:303-317 + gensim similarity, "
                       f"one forked worker per core",
             "single_process_value": single,
+            "compiled_c_port_value": c_port,      # oracle/scorer_oracle.c, all cores: not what the reference does
         }
 
     import torch
@@ -502,6 +512,38 @@ def run_own(args) -> None:
         lat = {"workload": "512 guesses x 8 slots, one host call (configs[1])",
                "p50_us": float(ts[len(ts) // 2]), "p99_us": float(ts[int(len(ts) * 0.99)])}
 
+    # ---- the Python boundary itself: 256 concurrent 2-word requests through the MicroBatcher ----
+    py_lat = None
+    if rank == 0 and world == 1 and not args.no_other_shapes:
+        import asyncio
+        from cassmantle_b200.backend import Backend
+        from cassmantle_b200.server import MicroBatcher
+        from cassmantle_b200.vocab import Vocabulary
+        n_keys = 200_000
+        keys = [f"w{i:x}" for i in range(n_keys)]
+        be = Backend(eng, Vocabulary(keys), min_score=MIN_SCORE)
+        rng = np.random.default_rng(5)
+        reqs = [{"3": {"input": keys[int(rng.integers(0, n_keys))].upper(), "answer": keys[11]},
+                 "9": {"input": keys[int(rng.integers(0, n_keys))], "answer": keys[22]}} for _ in range(256)]
+
+        async def one_round(mb):
+            t1 = time.perf_counter()
+            await asyncio.gather(*[mb.compute_scores(r) for r in reqs])
+            return time.perf_counter() - t1
+
+        async def rounds():
+            mb = MicroBatcher(be, max_batch=512, max_delay_s=0.0005)
+            ts2 = [await one_round(mb) for _ in range(30)]
+            mb.close()
+            return ts2, mb.batches
+
+        ts2, n_batches = asyncio.run(rounds())
+        ts2 = np.sort(np.asarray(ts2[5:])) * 1e3
+        py_lat = {"workload": "256 concurrent compute_scores requests x 2 words (strings), MicroBatcher + Backend",
+                  "p50_ms": float(ts2[len(ts2) // 2]), "p99_ms": float(ts2[-1]), "device_batches_per_round": n_batches / 30}
+        eng.set_answers(ans)
+        eng.synchronize()
+
     clocks = sampler.stop()
 
     # ---- parity spot check of the timed path against the CPU sample ----------------------
@@ -528,7 +570,7 @@ def run_own(args) -> None:
                        "l2": f"ring of {RING} distinct batches over a 3.6 GB table (inputs >> L2)"},
             "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
             "cpu_baseline": cpu_baseline, "clocks": clocks, "latency": lat, "parity": parity,
-            "other_shapes": other,
+            "other_shapes": other, "python_boundary": py_lat,
         }
         print(json.dumps(line), flush=True)
     if gather is not None:
