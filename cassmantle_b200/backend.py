@@ -62,38 +62,30 @@ class Backend:
         if not pairs:
             return []
         B = len(pairs)
-        lookup = self.vocab.lookup
-        words: List[List[str]] = []
-        exact = np.zeros(B, dtype=np.uint8)
-        ans_rows: List[int] = []
-        for b, (inputs, answer) in enumerate(pairs):
-            inputs, answer = inputs.lower(), answer.lower()          # backend.py:304
-            exact[b] = inputs == answer                              # backend.py:305
-            if self.phrase_guesses:
-                w = inputs.split()[: self.max_words]
-            else:
-                w = [inputs]
-            words.append(w)
-            ans_rows.append(lookup(answer))
-        N = max(1, max(len(w) for w in words))
-        idx = np.full((B, N), -1, dtype=np.int32)
-        length = np.zeros(B, dtype=np.int32)
-        for b, w in enumerate(words):
-            length[b] = len(w)
-            for k, t in enumerate(w):
-                idx[b, k] = lookup(t)
+        get = self.vocab.key_to_index.get
+        guesses = [p[0].lower() for p in pairs]                       # backend.py:304
+        answers = [p[1].lower() for p in pairs]
+        exact = np.fromiter((g == a for g, a in zip(guesses, answers)), dtype=np.uint8, count=B)  # :305
+        ans_rows = [get(a, -1) for a in answers]
+        if not self.phrase_guesses:                                   # the reference: whole string = one key
+            idx = np.fromiter((get(g, -1) for g in guesses), dtype=np.int32, count=B).reshape(B, 1)
+            length = np.ones(B, dtype=np.int32)
+        else:
+            words = [g.split()[: self.max_words] for g in guesses]
+            N = max(1, max(len(w) for w in words))
+            idx = np.full((B, N), -1, dtype=np.int32)
+            length = np.zeros(B, dtype=np.int32)
+            for b, w in enumerate(words):
+                length[b] = len(w)
+                for k, t in enumerate(w):
+                    idx[b, k] = get(t, -1)
         slots = np.asarray(self._slots_for(ans_rows), dtype=np.int32)
         scores, _ = self.engine.score_host(idx, length, slots, exact, self.min_score)
         floor32 = np.float32(self.min_score)
-        out = []
-        for b in range(B):
-            if exact[b]:
-                out.append(1.0)
-            elif scores[b] > floor32:
-                out.append(scores[b])            # numpy.float32, like wv.similarity's result
-            else:
-                out.append(self.min_score)       # the Python float, like max(min_score, .)
-        return out
+        keep = scores > floor32                  # the cosine wins max(min_score, score) only if greater
+        # numpy.float32 like wv.similarity's result, or the Python floats 1.0 / min_score
+        return [1.0 if e else (s if k else self.min_score)
+                for e, k, s in zip(exact.tolist(), keep.tolist(), list(scores))]
 
     # ---- the reference's two methods ---------------------------------------------------
     def compute_score(self, inputs: str, answer: str) -> float:
