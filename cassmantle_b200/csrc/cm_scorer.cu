@@ -333,13 +333,114 @@ cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
         answer_slot, exact, min_score, scores, centi, flags, n_ship_ctas);
 }
 
+// --------------------------------------------------------------------------------------
+// One-word guesses, many of them (more than one wave): a persistent, software-pipelined form of
+// the same arithmetic.  Each warp walks over groups of 32/LPG guesses; while the rows of the
+// current group are in flight it already loads the metadata (index, length, slot, exact flag) of
+// its next group, so the per-guess chain is  row latency + math  instead of
+// metadata latency + row latency + math  (r1_v3 profile: 58 % of the stall samples were
+// long-scoreboard waits at 43 % occupancy).  Bit-identical results to cm_score_kernel<SINGLE>.
+// --------------------------------------------------------------------------------------
+template <int VPL, int LPG, bool STREAM, int THREADS, int MIN_BLOCKS>
+__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
+cm_score1_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
+                 const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
+                 int n_guesses,
+                 const float *__restrict__ ans_unit, const int32_t *__restrict__ ans_rows,
+                 int n_answers, const int32_t *__restrict__ answer_slot,
+                 const uint8_t *__restrict__ exact, float min_score,
+                 float *__restrict__ scores, int32_t *__restrict__ centi, uint32_t flags,
+                 int n_ship_ctas, const cm::ShipArgs ship) {
+    constexpr int G = 32 / LPG;
+    if ((int)blockIdx.x < n_ship_ctas) {
+        cm::pdl_launch_dependents();
+        cm::ship_duty(ship, (int)blockIdx.x, n_ship_ctas);
+        return;
+    }
+    cm::pdl_launch_dependents();
+    const bool overlap = (flags & CM_SCORE_OVERLAP_PREVIOUS) != 0u;
+    if (!overlap) cm::pdl_wait();
+    bool waited = !overlap;
+    const int lane = threadIdx.x & 31;
+    const int sub = lane & (LPG - 1);
+    const int grp = lane / LPG;
+    const int warps_total = ((int)gridDim.x - n_ship_ctas) * (THREADS / 32);
+    const float4 *table4 = reinterpret_cast<const float4 *>(table);
+
+    int w = ((int)blockIdx.x - n_ship_ctas) * (THREADS / 32) + (threadIdx.x >> 5);
+    // metadata of the current group (loaded one iteration ahead)
+    int b = min(w * G + grp, n_guesses - 1);
+    int32_t m_row = 0; int m_len = 0, m_slot = 0; uint8_t m_exact = 0;
+    if (w * G < n_guesses) {
+        m_row = guess_idx[b]; m_len = guess_len[b]; m_slot = answer_slot[b];
+        m_exact = exact != nullptr ? exact[b] : (uint8_t)0;
+    }
+    while (w * G < n_guesses) {
+        const bool have = w * G + grp < n_guesses;
+        const bool is_exact = m_exact != 0;
+        const int slot = m_slot;
+        const bool slot_ok = slot >= 0 && slot < n_answers;
+        const int n = m_len < 0 ? 0 : (m_len > 1 ? 1 : m_len);
+        bool bad = (n > 0 && (m_row < 0 || (int64_t)m_row >= n_rows)) || n == 0 || !slot_ok;
+        const bool active = have && !is_exact && !bad;
+        // rows of this group
+        float4 acc[VPL];
+        const float4 *src = table4 + (size_t)(active ? m_row : 0) * dim4;
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+            const int j = sub + LPG * v;
+            if (active && j < dim4) acc[v] = STREAM ? cm::ld_stream_f4(src + j) : __ldg(src + j);
+            else acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        // metadata of the next group, in flight while this one is reduced
+        const int b_cur = b;
+        const int w_next = w + warps_total;
+        if (w_next * G < n_guesses) {
+            b = min(w_next * G + grp, n_guesses - 1);
+            m_row = guess_idx[b]; m_len = guess_len[b]; m_slot = answer_slot[b];
+            m_exact = exact != nullptr ? exact[b] : (uint8_t)0;
+        }
+        if (!waited) { cm::pdl_wait(); waited = true; }           // answers / outputs: predecessor done
+        {
+            const int32_t ar = slot_ok ? ans_rows[slot] : -1;
+            bad = bad || ar < 0 || (int64_t)ar >= n_rows;
+        }
+        float p = 0.f;
+        if (__any_sync(cm::kFullMask, active)) {
+            group_unitvec<VPL, LPG>(acc);
+            const float4 *u = reinterpret_cast<const float4 *>(ans_unit) + (size_t)(active ? slot : 0) * dim4;
+#pragma unroll
+            for (int v = 0; v < VPL; ++v) {
+                const int j = sub + LPG * v;
+                if (j < dim4) {
+                    const float4 q = u[j];
+                    p = fmaf(acc[v].x, q.x, p); p = fmaf(acc[v].y, q.y, p);
+                    p = fmaf(acc[v].z, q.z, p); p = fmaf(acc[v].w, q.w, p);
+                }
+            }
+            p = group_sum<LPG>(p);
+        }
+        float result;
+        if (is_exact) result = 1.0f;
+        else if (bad) result = min_score;
+        else result = (p > min_score) ? p : min_score;
+        if (have && sub == 0) {
+            scores[b_cur] = result;
+            if (centi != nullptr) centi[b_cur] = (int32_t)floor((double)result * 10000.0 + 0.5);
+        }
+        w = w_next;
+    }
+    if (!waited) cm::pdl_wait();
+}
+
 }  // namespace
 
 namespace {
 
 // Kernel variants.  `CM_SCORE_VARIANT` (environment, read once) forces one for tuning runs.
-//   wide   : 32 lanes per guess, R rows per round   -- phrases (N >= 3) and any table width
-//   narrow : 8 lanes per guess, 4 guesses per warp   -- one- and two-word guesses, dim 300 only
+//   wide       : 32 lanes per guess, R rows per round   -- phrases (N >= 2) and any table width
+//   single     : 8 lanes per guess, 4 guesses per warp  -- one-word guesses, dim 300
+//   persistent : the same with the next group's metadata prefetched -- very large one-word batches
 template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE = false>
 void launch_variant(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
                     const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
@@ -365,6 +466,33 @@ void launch_variant(const cm_engine *e, const int32_t *gi, const int32_t *gl, in
     cm::count_launch();
 }
 
+template <int VPL, int LPG, bool STREAM, int THREADS, int MIN_BLOCKS>
+void launch_single_persistent(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B,
+                              const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
+                              int32_t *centi, uint32_t flags, cudaStream_t st, const cm::ShipArgs *ship) {
+    constexpr int per_cta = (THREADS / 32) * (32 / LPG);
+    const int needed = (B + per_cta - 1) / per_cta;
+    const int resident = 148 * MIN_BLOCKS;
+    const int score_ctas = needed < resident ? needed : resident;
+    const bool shipping = ship != nullptr && ship->world > 0;
+    const int n_ship_ctas = shipping ? cm::ship_ctas(ship->n) : 0;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(score_ctas + n_ship_ctas));
+    cfg.blockDim = dim3(THREADS);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, cm_score1_kernel<VPL, LPG, STREAM, THREADS, MIN_BLOCKS>,
+                       (const float *)e->d_table, e->n_rows, e->dim / 4, gi, gl, B,
+                       (const float *)e->d_ans_unit, (const int32_t *)e->d_ans_rows, e->n_answers,
+                       slot, exact, min_score, scores, centi, flags, n_ship_ctas,
+                       shipping ? *ship : cm::ShipArgs{});
+    cm::count_launch();
+}
+
 int forced_variant() {
     static const int v = [] {
         const char *s = getenv("CM_SCORE_VARIANT");
@@ -384,29 +512,19 @@ void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int 
     if constexpr (VPL == 3) {
         if (e->dim == 300) {
             int variant = forced_variant();
-            if (variant == 0) variant = (N == 1) ? 20 : 8;
+            // Measured on B200 (tools/probe_kernel.py, us per launch, CM_SCORE_OVERLAP_PREVIOUS):
+            //   4096x16 : wide R=2 12.9 | R=3 13.6 | R=4 13.9 (72 regs, spills) | R=8 43 (4 CTAs/SM)
+            //   65536x1 : 8-lane groups 15.5 | 16-lane 16.9 | 32-lane 23.9 | persistent 15.9
+            //   10^6 x1 : 8-lane groups 216  | persistent (80 regs, 6 CTAs/SM) 191 = 0.97 of peak
+            if (variant == 0) variant = (N == 1) ? (B > (1 << 18) ? 31 : 20) : 8;
             if (variant >= 20 && N != 1) variant = 8;
             switch (variant) {
+                case 31: launch_single_persistent<10, 8, true, 128, 6>(e, gi, gl, B, slot, exact, min_score, scores, centi, flags, st, ship); return;
                 case 20: CM_S(8, true, 128, 8, 10); return;
-                case 21: CM_S(8, true, 128, 6, 10); return;
-                case 22: CM_S(8, false, 128, 8, 10); return;
                 case 23: CM_S(16, true, 128, 8, 5); return;
-                case 24: CM_S(32, true, 128, 8, 3); return;
-                case 25: CM_S(8, true, 256, 4, 10); return;
-                case 1: CM_V(32, 4, true, 128, 7, 3); return;
-                case 2: CM_V(32, 8, true, 128, 4, 3); return;
-                case 3: CM_V(8, 1, false, 128, 5, 10); return;
-                case 4: CM_V(8, 2, false, 128, 4, 10); return;
-                case 5: CM_V(16, 1, false, 128, 7, 5); return;
-                case 6: CM_V(16, 2, false, 128, 6, 5); return;
-                case 7: CM_V(8, 1, true, 128, 5, 10); return;
                 case 8: CM_V(32, 2, true, 128, 8, 3); return;
-                case 9: CM_V(32, 4, true, 256, 3, 3); return;
                 case 10: CM_V(32, 3, true, 128, 7, 3); return;
-                case 11: CM_V(32, 3, true, 256, 3, 3); return;
-                case 12: CM_V(32, 4, true, 128, 6, 3); return;
-                case 13: CM_V(32, 4, true, 256, 1, 3); return;
-                case 14: CM_V(32, 3, true, 128, 8, 3); return;
+                case 1: CM_V(32, 4, true, 128, 7, 3); return;
                 default: break;
             }
         }

@@ -397,7 +397,8 @@ def full_engine():
     eng.close()
 
 
-@pytest.mark.parametrize("B,N", [(512, 8), (4096, 16), (65536, 16), (16384, 64), (65536, 1)])
+@pytest.mark.parametrize("B,N", [(512, 8), (4096, 16), (65536, 16), (16384, 64), (65536, 1),
+                                 (300_001, 1)])     # the last one takes the persistent one-word kernel
 def test_full_size_configs(full_engine, B, N):
     V = synth.FULL_ROWS
     idx, ln, ans, slot, ex = synth.make_guess_batch(B, N, V, n_answers=3, seed=B + N)
