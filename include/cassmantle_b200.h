@@ -105,7 +105,8 @@ int cm_set_answers_device(cm_engine *e, const int32_t *d_answer_rows, int n_answ
  * d_exact may be NULL (no exact matches).  d_centi may be NULL; when given it receives
  * floor(score * 1e4 + 0.5), the browser's (score*100).toFixed(2) in hundredths
  * (static/script.js:300).  Asynchronous on `stream`; inputs and outputs stay in HBM.
- * `flags`: 0, or CM_SCORE_OVERLAP_PREVIOUS (see above).                                   */
+ * `flags`: 0, or CM_SCORE_OVERLAP_PREVIOUS (see above).  The call only enqueues a kernel,
+ * so a run of such calls can be captured in a CUDA graph and replayed (tested).            */
 int cm_score_batch_device(cm_engine *e,
                           const int32_t *d_guess_idx, const int32_t *d_guess_len,
                           int n_guesses, int n_slots,
