@@ -54,7 +54,9 @@ class Backend:
             for r in new:
                 self._answer_slot[r] = len(self._answer_rows)
                 self._answer_rows.append(r)
-            self.engine.set_answers(self._answer_rows)
+        # a no-op unless the registered set changed -- here or behind our back (another user of
+        # the engine, e.g. DeviceVocabulary.score_words, re-registers answers too)
+        self.engine.set_answers(self._answer_rows)
         return [self._answer_slot[r] for r in rows]
 
     # ---- core: a list of (guess, answer) string pairs -> reference-typed scores ------

@@ -24,6 +24,8 @@ class OracleEngine:
         self.set_calls = 0
 
     def set_answers(self, rows, stream=0):
+        if self.answers is not None and tuple(self.answers.tolist()) == tuple(int(r) for r in rows):
+            return                                   # the real engine skips an unchanged set too
         self.answers = np.asarray(rows, dtype=np.int32)
         self.set_calls += 1
 

@@ -116,3 +116,18 @@ def test_large_vocabulary_every_key_found():
         want = np.r_[np.arange(0, n, 3), np.arange(1, n, 5), [-1, -1, -1]].astype(np.int32)
         assert np.array_equal(got, want)
         dv.close()
+
+
+def test_backend_and_device_vocabulary_share_an_engine(vocab_stack, small_engine, small_table):
+    """Both register answers with the engine; interleaving them must not leave stale slots behind."""
+    from cassmantle_b200.backend import Backend
+    from cassmantle_b200.vocab import Vocabulary
+    dv, keys = vocab_stack
+    be = Backend(small_engine, Vocabulary(keys), min_score=0.01)
+    ref = O.OracleBackend(O.OracleWordVectors(small_table, keys), 0.01)
+    for i in range(3):
+        a = float(be.compute_score(keys[100 + i], keys[200]))
+        dv.score_words([keys[1]], [keys[300 + i]], [0], 0.01)          # re-registers other answers
+        b = float(be.compute_score(keys[100 + i], keys[200]))
+        want = float(ref.compute_score(keys[100 + i], keys[200]))
+        assert a == b and abs(a - want) <= COS_TOL
