@@ -323,142 +323,151 @@ def run_own(args) -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    # The timed phases run once; if the clock record shows a thermal / hardware slowdown they are
+    # run a second time and that measurement is the one reported (sw_power_cap is only noted).
+    pipe = None
+    for attempt in range(2):
+        sampler = ClockSampler(local_rank)
+        sampler.start()
 
-    # ---- value: device-resident, K steps ------------------------------------------------
-    for i in range(args.warmup):
-        step_device(i)
-    barrier()
-    launches0 = lib.cm_kernel_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    t_enq = time.perf_counter()
-    for i in range(args.steps):
-        step_device(args.warmup + i)
-    e1.record(stream)
-    t_enq = time.perf_counter() - t_enq
-    barrier()
-    gpu_launches = int(lib.cm_kernel_launch_count() - launches0)
-    dev_ms = max_over_ranks(e0.elapsed_time(e1))
-    value = args.steps * B * world / (dev_ms * 1e-3)
+        # ---- value: device-resident, K steps ------------------------------------------------
+        for i in range(args.warmup):
+            step_device(i)
+        barrier()
+        launches0 = lib.cm_kernel_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        t_enq = time.perf_counter()
+        for i in range(args.steps):
+            step_device(args.warmup + i)
+        e1.record(stream)
+        t_enq = time.perf_counter() - t_enq
+        barrier()
+        gpu_launches = int(lib.cm_kernel_launch_count() - launches0)
+        dev_ms = max_over_ranks(e0.elapsed_time(e1))
+        value = args.steps * B * world / (dev_ms * 1e-3)
 
-    # every rank must now hold every rank's scores of the last step (checked against a local
-    # re-score of the peers' batches, which are seeded by rank)
-    gather_check = None
-    if gather is not None:
-        ptr = gather.wait(st)          # ships the last step (no launch follows it) and waits for all ranks
+        # every rank must now hold every rank's scores of the last step (checked against a local
+        # re-score of the peers' batches, which are seeded by rank)
+        gather_check = None
+        if gather is not None:
+            ptr = gather.wait(st)          # ships the last step (no launch follows it) and waits for all ranks
+            torch.cuda.synchronize()
+            got = gather.as_tensor(ptr).cpu().numpy()
+            last = (args.warmup + args.steps - 1) % RING
+            ok = gather.timed_out() == 0
+            for r in range(world):
+                _, ring_r = make_ring(1000 + 7919 * r)
+                idx_r, ln_r, slot_r, ex_r = ring_r[last]
+                want_r, _ = eng.score_host(idx_r, ln_r, slot_r, ex_r, MIN_SCORE)
+                ok = ok and bool(np.array_equal(got[r, :B].view(np.uint32), want_r.view(np.uint32)))
+            if os.environ.get("CM_GATHER_TRACE") and rank == 0:
+                tr = np.zeros(512, dtype=np.uint64)
+                lib.cm_gather_trace(gather._h, tr.ctypes.data)
+                tr = tr.reshape(64, 8)
+                tr = tr[np.argsort(tr[:, 0])]
+                for row in tr[-12:]:
+                    b0 = int(row[1])
+                    print("trace step", int(row[0]), "start", b0 % 10**9, "order", int(row[2]) - b0, "stores", int(row[3]) - b0,
+                          "fence", int(row[4]) - b0, "flags", int(row[5]) - b0, "peers", int(row[6]) - b0, file=sys.stderr)
+            t_ok = torch.tensor([1.0 if ok else 0.0], device=dev)
+            dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+            gather_check = bool(t_ok.item() == 1.0)
+
+        # ---- roofline: the scoring kernel alone, >= ~1 s of launches -------------------------
+        per_step_ms = max(dev_ms / args.steps, 1e-3)
+        n_roof = int(min(200_000, max(2000, args.roofline_s * 1e3 / per_step_ms)))
+        fn, h = lib.cm_score_batch_device, eng._h
+        for i in range(50):
+            p = t_ring[i % RING]
+            fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
         torch.cuda.synchronize()
-        got = gather.as_tensor(ptr).cpu().numpy()
-        last = (args.warmup + args.steps - 1) % RING
-        ok = gather.timed_out() == 0
-        for r in range(world):
-            _, ring_r = make_ring(1000 + 7919 * r)
-            idx_r, ln_r, slot_r, ex_r = ring_r[last]
-            want_r, _ = eng.score_host(idx_r, ln_r, slot_r, ex_r, MIN_SCORE)
-            ok = ok and bool(np.array_equal(got[r, :B].view(np.uint32), want_r.view(np.uint32)))
-        if os.environ.get("CM_GATHER_TRACE") and rank == 0:
-            tr = np.zeros(512, dtype=np.uint64)
-            lib.cm_gather_trace(gather._h, tr.ctypes.data)
-            tr = tr.reshape(64, 8)
-            tr = tr[np.argsort(tr[:, 0])]
-            for row in tr[-12:]:
-                b0 = int(row[1])
-                print("trace step", int(row[0]), "start", b0 % 10**9, "order", int(row[2]) - b0, "stores", int(row[3]) - b0,
-                      "fence", int(row[4]) - b0, "flags", int(row[5]) - b0, "peers", int(row[6]) - b0, file=sys.stderr)
-        t_ok = torch.tensor([1.0 if ok else 0.0], device=dev)
-        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
-        gather_check = bool(t_ok.item() == 1.0)
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r0.record(stream)
+        for i in range(n_roof):
+            p = t_ring[i % RING]
+            fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
+        r1.record(stream)
+        torch.cuda.synchronize()
+        kern_us = r0.elapsed_time(r1) * 1e3 / n_roof
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            with open(peaks_path) as f:
+                peak, peak_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        else:
+            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+        achieved = B * BYTES_PER_GUESS / (kern_us * 1e-6) / 1e9
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": TRAFFIC_BYTES_PER_LAUNCH,
+                    "kernel": "cm_score_kernel<VPL=3,LPG=32,R=2> (4096x16 launches, CM_SCORE_OVERLAP_PREVIOUS)", "kernel_us": kern_us, "launches_timed": n_roof,
+                    "algorithmic_bytes_per_launch": B * BYTES_PER_GUESS, "peak_source": peak_src}
 
-    # ---- roofline: the scoring kernel alone, >= ~1 s of launches -------------------------
-    per_step_ms = max(dev_ms / args.steps, 1e-3)
-    n_roof = int(min(200_000, max(2000, args.roofline_s * 1e3 / per_step_ms)))
-    fn, h = lib.cm_score_batch_device, eng._h
-    for i in range(50):
-        p = t_ring[i % RING]
-        fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
-    torch.cuda.synchronize()
-    r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    r0.record(stream)
-    for i in range(n_roof):
-        p = t_ring[i % RING]
-        fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
-    r1.record(stream)
-    torch.cuda.synchronize()
-    kern_us = r0.elapsed_time(r1) * 1e3 / n_roof
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        with open(peaks_path) as f:
-            peak, peak_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
-    else:
-        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    achieved = B * BYTES_PER_GUESS / (kern_us * 1e-6) / 1e9
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": TRAFFIC_BYTES_PER_LAUNCH,
-                "kernel": "cm_score_kernel<VPL=3,LPG=32,R=2> (4096x16 launches, CM_SCORE_OVERLAP_PREVIOUS)", "kernel_us": kern_us, "launches_timed": n_roof,
-                "algorithmic_bytes_per_launch": B * BYTES_PER_GUESS, "peak_source": peak_src}
+        # ---- e2e: host buffers through the C ABI ---------------------------------------------
+        # (a) pipelined: cm_pipe_* with PIPE_DEPTH batches in flight.  The ring's batches live in
+        #     page-locked host memory (the pipe's slots, filled before the timed region); every
+        #     step DMAs that step's inputs to the GPU, scores them, and the step's scores land
+        #     back in page-locked host memory, where the host reads them.
+        # (b) synchronous: one cm_score_batch_host call per step (what Backend.compute_scores uses).
+        from cassmantle_b200.engine import ScoringPipe
+        if pipe is None:
+            pipe = ScoringPipe(eng, depth=RING, max_guesses=B, max_slots=N)
+            views = []
+            for s_i, (idx, ln, slot, ex) in enumerate(ring):
+                v = pipe.buffers(s_i, B, N)
+                v["guess_idx"][:] = idx
+                v["guess_len"][:] = ln
+                v["answer_slot"][:] = slot
+                v["exact"][:] = ex
+                views.append(v)
+        submit, wait, ph = lib.cm_pipe_submit, lib.cm_pipe_wait, pipe._h
+        checksum = 0.0
 
-    # ---- e2e: host buffers through the C ABI ---------------------------------------------
-    # (a) pipelined: cm_pipe_* with PIPE_DEPTH batches in flight.  The ring's batches live in
-    #     page-locked host memory (the pipe's slots, filled before the timed region); every
-    #     step DMAs that step's inputs to the GPU, scores them, and the step's scores land
-    #     back in page-locked host memory, where the host reads them.
-    # (b) synchronous: one cm_score_batch_host call per step (what Backend.compute_scores uses).
-    from cassmantle_b200.engine import ScoringPipe
-    pipe = ScoringPipe(eng, depth=RING, max_guesses=B, max_slots=N)
-    views = []
-    for s_i, (idx, ln, slot, ex) in enumerate(ring):
-        v = pipe.buffers(s_i, B, N)
-        v["guess_idx"][:] = idx
-        v["guess_len"][:] = ln
-        v["answer_slot"][:] = slot
-        v["exact"][:] = ex
-        views.append(v)
-    submit, wait, ph = lib.cm_pipe_submit, lib.cm_pipe_wait, pipe._h
-    checksum = 0.0
-
-    def run_pipe(first: int, count: int) -> None:
-        nonlocal checksum
-        for i in range(first, first + count):
-            if i - first >= PIPE_DEPTH:
-                j = (i - PIPE_DEPTH) % RING
+        def run_pipe(first: int, count: int) -> None:
+            nonlocal checksum
+            for i in range(first, first + count):
+                if i - first >= PIPE_DEPTH:
+                    j = (i - PIPE_DEPTH) % RING
+                    wait(ph, j)
+                    checksum += float(views[j]["scores"][0])       # the host consumes the result
+                if submit(ph, i % RING, ms32, 0) != 0:
+                    _lib.check(-1)
+            for i in range(max(first, first + count - PIPE_DEPTH), first + count):
+                j = i % RING
                 wait(ph, j)
-                checksum += float(views[j]["scores"][0])       # the host consumes the result
-            if submit(ph, i % RING, ms32, 0) != 0:
-                _lib.check(-1)
-        for i in range(max(first, first + count - PIPE_DEPTH), first + count):
-            j = i % RING
-            wait(ph, j)
-            checksum += float(views[j]["scores"][0])
+                checksum += float(views[j]["scores"][0])
 
-    run_pipe(0, max(args.warmup, PIPE_DEPTH))
-    barrier()
-    launches1 = lib.cm_kernel_launch_count()
-    t0 = time.perf_counter()
-    run_pipe(args.warmup, args.steps)
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
-    e2e_launches = int(lib.cm_kernel_launch_count() - launches1)
-    h2d = B * N * 4 + B * 4 + B * 4 + B
-    e2e = {"value": args.steps * B * world / e2e_s, "unit": UNIT,
-           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 4,
-           "ms_per_step": e2e_s / args.steps * 1e3, "gpu_launches": e2e_launches,
-           "api": f"cm_pipe_submit/cm_pipe_wait (C ABI), {PIPE_DEPTH} batches in flight, inputs DMA'd "
-                  f"from page-locked host slots, scores written back into them by the kernel"}
-    for i in range(args.warmup):
-        step_host(i)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    n_sync = min(args.steps, 2000)
-    for i in range(n_sync):
-        step_host(args.warmup + i)
-    sync_s = time.perf_counter() - t0
-    e2e["synchronous_call"] = {"value": n_sync * B / sync_s, "unit": UNIT, "ms_per_step": sync_s / n_sync * 1e3,
-                               "api": "cm_score_batch_host, one blocking call per step, pinned buffers"}
-    # parity of the pipelined path against the synchronous one on a few slots
-    for j in range(3):
-        step_host(j)
-        assert np.array_equal(h_scores_np.view(np.uint32),
-                              np.asarray(views[j]["scores"]).view(np.uint32)) or args.steps < RING
+        run_pipe(0, max(args.warmup, PIPE_DEPTH))
+        barrier()
+        launches1 = lib.cm_kernel_launch_count()
+        t0 = time.perf_counter()
+        run_pipe(args.warmup, args.steps)
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
+        e2e_launches = int(lib.cm_kernel_launch_count() - launches1)
+        h2d = B * N * 4 + B * 4 + B * 4 + B
+        e2e = {"value": args.steps * B * world / e2e_s, "unit": UNIT,
+               "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 4,
+               "ms_per_step": e2e_s / args.steps * 1e3, "gpu_launches": e2e_launches,
+               "api": f"cm_pipe_submit/cm_pipe_wait (C ABI), {PIPE_DEPTH} batches in flight, inputs DMA'd "
+                      f"from page-locked host slots, scores written back into them by the kernel"}
+        for i in range(args.warmup):
+            step_host(i)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        n_sync = min(args.steps, 2000)
+        for i in range(n_sync):
+            step_host(args.warmup + i)
+        sync_s = time.perf_counter() - t0
+        e2e["synchronous_call"] = {"value": n_sync * B / sync_s, "unit": UNIT, "ms_per_step": sync_s / n_sync * 1e3,
+                                   "api": "cm_score_batch_host, one blocking call per step, pinned buffers"}
+        # parity of the pipelined path against the synchronous one on a few slots
+        for j in range(3):
+            step_host(j)
+            assert np.array_equal(h_scores_np.view(np.uint32),
+                                  np.asarray(views[j]["scores"]).view(np.uint32)) or args.steps < RING
+
+        timed_clocks = sampler.stop()
+        if not (set(timed_clocks["reasons"]) & set(ClockSampler.BAD)):
+            break
 
     # ---- the other BASELINE.json shapes, kernel only (N = 1 is the only shape
     #      the reference itself produces; the seq-N shapes are the labelled mean-pool extension)
@@ -563,7 +572,7 @@ def run_own(args) -> None:
         eng.set_answers(ans)
         eng.synchronize()
 
-    clocks = sampler.stop()
+    clocks = dict(timed_clocks, remeasured=bool(attempt))
 
     # ---- parity spot check of the timed path against the CPU sample ----------------------
     parity = None

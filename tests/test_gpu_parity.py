@@ -174,6 +174,34 @@ def test_overlapped_launches_match_serial(small_engine):
         assert np.array_equal(outs[i].cpu().numpy().view(np.uint32), want[i].view(np.uint32)), i
 
 
+def test_host_entry_point_from_several_threads(small_engine):
+    """ctypes releases the GIL: concurrent callers of the blocking entry point take turns on the
+    engine's staging block and every one gets its own scores back."""
+    import threading
+    ans = np.array([42, 4242], np.int32)
+    small_engine.set_answers(ans)
+    small_engine.synchronize()
+    jobs = []
+    for t in range(6):
+        idx, ln, _, slot, ex = synth.make_guess_batch(700 + 13 * t, 1 + t % 4, 50_000, 2, seed=800 + t, ragged=True)
+        jobs.append((idx, ln, slot, ex, small_engine.score_host(idx, ln, slot, ex, 0.01)[0]))
+    errors = []
+
+    def worker(job):
+        idx, ln, slot, ex, want = job
+        for _ in range(40):
+            got, _ = small_engine.score_host(idx, ln, slot, ex, 0.01)
+            if not np.array_equal(got.view(np.uint32), want.view(np.uint32)):
+                errors.append("mismatch")
+
+    threads = [threading.Thread(target=worker, args=(j,)) for j in jobs]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors
+
+
 def test_device_entry_point_in_a_cuda_graph(small_engine):
     """A run of scoring launches (programmatic-dependent-launch edges included) can be captured
     once and replayed: the launch-bound small shapes drop from ~4-5 us to ~2.8 us per step."""

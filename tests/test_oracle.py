@@ -141,3 +141,46 @@ def test_c_synth_fill_is_bit_identical_to_numpy():
     assert np.array_equal(a[rows].view(np.uint32), synth.table_rows(rows, 0).view(np.uint32))
     b = c_oracle.synth_fill(1000, 300, seed=9, threads=1)
     assert np.array_equal(b.view(np.uint32), synth.table_rows(np.arange(1000), 9).view(np.uint32))
+
+
+# ---- properties of the restated scorer (hypothesis) -------------------------------------------
+from hypothesis import given, settings, strategies as st   # noqa: E402
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.integers(0, 1999), st.integers(0, 1999), st.floats(0.01, 100.0))
+def test_similarity_properties(i, j, scale):
+    T = _prop_table()
+    s = float(O.similarity(T, i, j))
+    assert -1.0 - 1e-6 <= s <= 1.0 + 1e-6
+    assert s == float(O.similarity(T, j, i))                      # the fp32 dot is symmetric
+    T2 = T.copy()
+    T2[i] = (T2[i] * np.float32(scale)).astype(np.float32)        # cosine ignores the row's length
+    assert abs(float(O.similarity(T2, i, j)) - s) <= 5e-7
+    if i == j:
+        assert abs(s - 1.0) <= 5e-7
+
+
+@settings(max_examples=40, deadline=None)
+@given(st.lists(st.integers(0, 1999), min_size=1, max_size=12), st.integers(0, 1999), st.floats(-0.5, 0.9))
+def test_batch_scorers_agree_and_respect_the_floor(rows, ans, floor):
+    T = _prop_table()
+    idx = np.asarray([rows], dtype=np.int32)
+    ln = np.asarray([len(rows)], dtype=np.int32)
+    args = (T, idx, ln, np.asarray([ans], np.int32), np.asarray([0], np.int32), None, floor)
+    a = O.score_batch_faithful(*args)[0]
+    v = O.score_batch_vectorised(*args)[0]
+    c = c_oracle.score_batch(*args)[0]
+    f32 = np.float32(floor)
+    assert a >= f32 and v >= f32 and c >= f32
+    for other in (v, c):
+        assert abs(float(a) - float(other)) <= 1.5e-6 or (a == f32) != (other == f32) and abs(float(max(a, other)) - floor) <= 1.5e-6
+
+
+_PROP = {}
+
+
+def _prop_table():
+    if "t" not in _PROP:
+        _PROP["t"] = synth.full_table(2000, seed=11, threads=2)
+    return _PROP["t"]
