@@ -422,13 +422,17 @@ def run_own(args) -> None:
         submit, wait, ph = lib.cm_pipe_submit, lib.cm_pipe_wait, pipe._h
         checksum = 0.0
 
-        def run_pipe(first: int, count: int) -> None:
+        def run_pipe(first: int, count: int, fill: bool = False) -> None:
             nonlocal checksum
             for i in range(first, first + count):
                 if i - first >= PIPE_DEPTH:
                     j = (i - PIPE_DEPTH) % RING
                     wait(ph, j)
                     checksum += float(views[j]["scores"][0])       # the host consumes the result
+                if fill:         # a producer that has its batch elsewhere in host memory copies it in
+                    src, dst = h_np[(i + 1) % RING], views[i % RING]
+                    np.copyto(dst["guess_idx"], src[0]); np.copyto(dst["guess_len"], src[1])
+                    np.copyto(dst["answer_slot"], src[2]); np.copyto(dst["exact"], src[3])
                 if submit(ph, i % RING, ms32, 0) != 0:
                     _lib.check(-1)
             for i in range(max(first, first + count - PIPE_DEPTH), first + count):
@@ -449,6 +453,18 @@ def run_own(args) -> None:
                "ms_per_step": e2e_s / args.steps * 1e3, "gpu_launches": e2e_launches,
                "api": f"cm_pipe_submit/cm_pipe_wait (C ABI), {PIPE_DEPTH} batches in flight, inputs DMA'd "
                       f"from page-locked host slots, scores written back into them by the kernel"}
+        # (a') the same with the producer's copy into the slot inside the timed region
+        n_fill = min(args.steps, 1000)
+        run_pipe(0, PIPE_DEPTH, fill=True)
+        t0 = time.perf_counter()
+        run_pipe(7, n_fill, fill=True)
+        fill_s = time.perf_counter() - t0
+        e2e["with_host_fill"] = {"value": n_fill * B / fill_s, "unit": UNIT, "ms_per_step": fill_s / n_fill * 1e3,
+                                 "note": "as e2e, plus a 0.3 MB host copy of each batch into its slot per step "
+                                         "(rank-local figure)"}
+        for s_i, (idx, ln, slot, ex) in enumerate(ring):        # restore the slots' own batches
+            v = views[s_i]
+            v["guess_idx"][:] = idx; v["guess_len"][:] = ln; v["answer_slot"][:] = slot; v["exact"][:] = ex
         for i in range(args.warmup):
             step_host(i)
         torch.cuda.synchronize()

@@ -13,8 +13,8 @@
 //   one pass    out[x] = (acc*ww + (in[x-r-1] + in[x+r+1])*fw + 2^23) >> 24      (uint32 wrap)
 //               acc = sum of in[clamp(i)] for i in [x-r, x+r], r = int(r'),
 //               ww = (uint32)(2^24 / (2 r' + 1)),  fw = (2^24 - (2r+1) ww) / 2
-//   image       3 passes along x, then 3 passes along y (Pillow transposes, blurs along x
-//               again and transposes back -- the same thing)
+//   image       3 passes along x, transpose, 3 passes along x again, transpose back (what
+//               Pillow does for the y direction; it also keeps every pass coalesced here)
 //
 // The running accumulator of the C code becomes a per-line prefix sum in shared memory (exact:
 // it is an integer sum), so every output pixel of a line is computed independently.  One CTA
@@ -182,18 +182,57 @@ int launch_pass(cm_blur *b, const uint8_t *src, size_t src_req_stride, uint8_t *
     return CM_OK;
 }
 
+// Pixel transpose [h][w][C] -> [w][h][C] through a 32x32 shared-memory tile (Pillow's
+// ImagingTranspose): the blur along y then runs on contiguous lines like the blur along x.  A
+// strided column pass measured 351 us against 56 us for a row pass (1024x1024 RGB, 8 sessions).
+template <int C>
+__global__ void __launch_bounds__(256)
+cm_transpose_kernel(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, int h, int w, size_t req_stride) {
+    __shared__ uint8_t tile[32][32 * C + 4];
+    const uint8_t *in = src + blockIdx.z * req_stride;
+    uint8_t *out = dst + blockIdx.z * req_stride;
+    const int x0 = blockIdx.x * 32, y0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int r = ty; r < 32; r += 8) {
+        const int y = y0 + r, x = x0 + tx;
+        if (y < h && x < w) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) tile[r][tx * C + c] = in[((size_t)y * w + x) * C + c];
+        }
+    }
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+        const int x = x0 + r, y = y0 + tx;                   // output row x, output column y
+        if (x < w && y < h) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) out[((size_t)x * h + y) * C + c] = tile[tx][r * C + c];
+        }
+    }
+}
+
+template <int C>
+int launch_transpose(cm_blur *b, const uint8_t *src, uint8_t *dst, int h, int w, size_t req_stride, int batch) {
+    cm_transpose_kernel<C><<<dim3((unsigned)((w + 31) / 32), (unsigned)((h + 31) / 32), (unsigned)batch), 256, 0,
+                             b->stream>>>(src, dst, h, w, req_stride);
+    cm::count_launch();
+    CM_CUDA(cudaGetLastError());
+    return CM_OK;
+}
+
 template <int C>
 int blur_batch(cm_blur *b, int batch, uint8_t **result) {
     const size_t img = (size_t)b->h * b->w * C;
-    const size_t row = (size_t)b->w * C;
+    const size_t row = (size_t)b->w * C, col = (size_t)b->h * C;
     // along x: lines are rows
     if (int rc = launch_pass<C>(b, b->d_src, 0, b->d_a, img, b->h, b->w, row, C, batch)) return rc;
     if (int rc = launch_pass<C>(b, b->d_a, img, b->d_b, img, b->h, b->w, row, C, batch)) return rc;
     if (int rc = launch_pass<C>(b, b->d_b, img, b->d_a, img, b->h, b->w, row, C, batch)) return rc;
-    // along y: lines are columns
-    if (int rc = launch_pass<C>(b, b->d_a, img, b->d_b, img, b->w, b->h, C, row, batch)) return rc;
-    if (int rc = launch_pass<C>(b, b->d_b, img, b->d_a, img, b->w, b->h, C, row, batch)) return rc;
-    if (int rc = launch_pass<C>(b, b->d_a, img, b->d_b, img, b->w, b->h, C, row, batch)) return rc;
+    // along y: transpose, blur the (now contiguous) columns, transpose back -- as Pillow does
+    if (int rc = launch_transpose<C>(b, b->d_a, b->d_b, b->h, b->w, img, batch)) return rc;
+    if (int rc = launch_pass<C>(b, b->d_b, img, b->d_a, img, b->w, b->h, col, C, batch)) return rc;
+    if (int rc = launch_pass<C>(b, b->d_a, img, b->d_b, img, b->w, b->h, col, C, batch)) return rc;
+    if (int rc = launch_pass<C>(b, b->d_b, img, b->d_a, img, b->w, b->h, col, C, batch)) return rc;
+    if (int rc = launch_transpose<C>(b, b->d_a, b->d_b, b->w, b->h, img, batch)) return rc;
     *result = b->d_b;
     return CM_OK;
 }
