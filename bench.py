@@ -399,7 +399,7 @@ def run_own(args) -> None:
         achieved = B * BYTES_PER_GUESS / (kern_us * 1e-6) / 1e9
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": TRAFFIC_BYTES_PER_LAUNCH,
-                    "kernel": "cm_score_kernel<VPL=3,LPG=32,R=2> (4096x16 launches, CM_SCORE_OVERLAP_PREVIOUS)", "kernel_us": kern_us, "launches_timed": n_roof,
+                    "kernel": "cm_score_kernel<VPL=5,LPG=16,R=1> (4096x16 launches, CM_SCORE_OVERLAP_PREVIOUS)", "kernel_us": kern_us, "launches_timed": n_roof,
                     "algorithmic_bytes_per_launch": B * BYTES_PER_GUESS, "peak_source": peak_src}
 
         # ---- e2e: host buffers through the C ABI ---------------------------------------------
@@ -628,7 +628,7 @@ def run_own(args) -> None:
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of cm_score_kernel at 4096x16 from the
 # committed `ncu --set full` capture (profiles/).
-TRAFFIC_BYTES_PER_LAUNCH = 81_531_648   # profiles/r1_v3_4096x16.summary.txt (79.76 MB read + 1.77 MB written)
+TRAFFIC_BYTES_PER_LAUNCH = 81_622_272   # profiles/r1_v4_4096x16.summary.txt (79.76 MB read + 1.86 MB written)
 
 
 def main() -> None:

@@ -569,7 +569,8 @@ cm_score1_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
 namespace {
 
 // Kernel variants.  `CM_SCORE_VARIANT` (environment, read once) forces one for tuning runs.
-//   wide       : 32 lanes per guess, R rows per round   -- phrases (N >= 2) and any table width
+//   wide       : 32 lanes per guess, R rows per round   -- small phrase batches and any table width
+//   paired     : 16 lanes per guess, 2 guesses per warp -- bandwidth-bound phrase batches, dim 300
 //   single     : 8 lanes per guess, 4 guesses per warp  -- one-word guesses, dim 300
 //   persistent : the same with the next group's metadata prefetched -- very large one-word batches
 template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE = false>
@@ -678,7 +679,11 @@ void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int 
             //   4096x16 : wide R=2 12.9 | R=3 13.6 | R=4 13.9 (72 regs, spills) | R=8 43 (4 CTAs/SM)
             //   65536x1 : 8-lane groups 15.5 | 16-lane 16.9 | 32-lane 23.9 | persistent 15.9
             //   10^6 x1 : 8-lane groups 216  | persistent (80 regs, 6 CTAs/SM) 191 = 0.97 of peak
-            if (variant == 0) variant = (N == 1) ? (B > (1 << 18) ? 31 : 20) : 8;
+            //   phrases : 16-lane groups (2 guesses per warp, 5 float4 per lane, R=1) beat 32-lane R=2 once
+            //             the launch is bandwidth-bound -- 4096x16 11.6 vs 12.9, 65536x16 181 vs 200,
+            //             16384x8 24.1 vs 30.4 -- and lose when it is latency-bound (512x8 6.0 vs 3.8)
+            if (variant == 0)
+                variant = (N == 1) ? (B > (1 << 18) ? 31 : 20) : ((int64_t)B * N >= 32768 ? 6 : 8);
             if (variant >= 20 && variant < 40 && N != 1) variant = 8;
             switch (variant) {
                 case 40: launch_bulk<4, 128, 8>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st, ship); return;
@@ -687,6 +692,9 @@ void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int 
                 case 31: launch_single_persistent<10, 8, true, 128, 6>(e, gi, gl, B, slot, exact, min_score, scores, centi, flags, st, ship); return;
                 case 20: CM_S(8, true, 128, 8, 10); return;
                 case 23: CM_S(16, true, 128, 8, 5); return;
+                case 5: CM_V(16, 2, true, 128, 6, 5); return;
+                case 6: CM_V(16, 1, true, 128, 7, 5); return;
+                case 7: CM_V(8, 1, true, 128, 5, 10); return;
                 case 8: CM_V(32, 2, true, 128, 8, 3); return;
                 case 10: CM_V(32, 3, true, 128, 7, 3); return;
                 case 1: CM_V(32, 4, true, 128, 7, 3); return;
