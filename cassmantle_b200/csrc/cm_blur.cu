@@ -170,11 +170,9 @@ template <int C>
 int launch_pass(cm_blur *b, const uint8_t *src, size_t src_req_stride, uint8_t *dst, size_t dst_req_stride,
                 int n_lines, int n, size_t line_stride, size_t pix_stride, int batch) {
     const size_t smem = (size_t)C * (n + 1) * sizeof(uint32_t) + (size_t)n * C;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(cm_boxblur_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
-    }
+    // per device and cheap: set it on every launch rather than cache a process-wide flag
+    if (smem > 48 * 1024)
+        CM_CUDA(cudaFuncSetAttribute(cm_boxblur_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cm_boxblur_kernel<C><<<dim3((unsigned)n_lines, (unsigned)batch), 256, smem, b->stream>>>(
         src, src_req_stride, dst, dst_req_stride, n, line_stride, pix_stride, (const BoxParams *)b->d_params);
     cm::count_launch();

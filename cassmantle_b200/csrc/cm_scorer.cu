@@ -631,12 +631,9 @@ void launch_bulk(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B
                  int32_t *centi, uint32_t flags, cudaStream_t st, const cm::ShipArgs *ship) {
     constexpr int WARPS = THREADS / 32;
     const size_t smem = (size_t)WARPS * S * 1200 + (size_t)WARPS * S * 8;
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (smem > 48 * 1024)      // per device and cheap: no process-wide flag
         cudaFuncSetAttribute(cm_score_bulk_kernel<S, THREADS, MIN_BLOCKS>,
                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_set = true;
-    }
     const bool shipping = ship != nullptr && ship->world > 0;
     const int n_ship_ctas = shipping ? cm::ship_ctas(ship->n) : 0;
     cudaLaunchConfig_t cfg = {};

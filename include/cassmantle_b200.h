@@ -67,7 +67,7 @@ const char *cm_version(void);
  * Replaces `self.wv = KeyedVectors.load("data/word2vec.wordvectors", mmap='r')`,
  * src/backend.py:45: the n_rows x dim fp32 matrix becomes resident in the GPU's HBM.      */
 int cm_engine_create(cm_engine **out, int device, int64_t n_rows, int dim);
-int cm_engine_destroy(cm_engine *e);
+int cm_engine_destroy(cm_engine *e);   /* destroy its pipes, gathers and vocabularies first */
 
 /* Copy rows [row0, row0+n) of the host matrix (row-major fp32, e.g. a slice of gensim's
  * mmap'd `wv.vectors`) into the resident table.  Blocks until the copy is done.          */
