@@ -419,16 +419,22 @@ def run_own(args) -> None:
                 v["answer_slot"][:] = slot
                 v["exact"][:] = ex
                 views.append(v)
-        submit, wait, ph = lib.cm_pipe_submit, lib.cm_pipe_wait, pipe._h
+        submit, wait, cycle, ph = lib.cm_pipe_submit, lib.cm_pipe_wait, lib.cm_pipe_cycle, pipe._h
         checksum = 0.0
 
         def run_pipe(first: int, count: int, fill: bool = False) -> None:
             nonlocal checksum
             for i in range(first, first + count):
+                if not fill and i - first >= PIPE_DEPTH:               # steady state: one call per step
+                    j = (i - PIPE_DEPTH) % RING
+                    if cycle(ph, j, i % RING, ms32, 0) != 0:
+                        _lib.check(-1)
+                    checksum += float(views[j]["scores"][0])       # the host consumes the result
+                    continue
                 if i - first >= PIPE_DEPTH:
                     j = (i - PIPE_DEPTH) % RING
                     wait(ph, j)
-                    checksum += float(views[j]["scores"][0])       # the host consumes the result
+                    checksum += float(views[j]["scores"][0])
                 if fill:         # a producer that has its batch elsewhere in host memory copies it in
                     src, dst = h_np[(i + 1) % RING], views[i % RING]
                     np.copyto(dst["guess_idx"], src[0]); np.copyto(dst["guess_len"], src[1])
@@ -451,7 +457,7 @@ def run_own(args) -> None:
         e2e = {"value": args.steps * B * world / e2e_s, "unit": UNIT,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 4,
                "ms_per_step": e2e_s / args.steps * 1e3, "gpu_launches": e2e_launches,
-               "api": f"cm_pipe_submit/cm_pipe_wait (C ABI), {PIPE_DEPTH} batches in flight, inputs DMA'd "
+               "api": f"cm_pipe_cycle = cm_pipe_wait + cm_pipe_submit (C ABI), {PIPE_DEPTH} batches in flight, inputs DMA'd "
                       f"from page-locked host slots, scores written back into them by the kernel"}
         # (a') the same with the producer's copy into the slot inside the timed region
         n_fill = min(args.steps, 1000)

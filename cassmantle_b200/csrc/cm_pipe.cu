@@ -160,6 +160,14 @@ int cm_pipe_wait(cm_pipe *p, int slot) {
     return CM_OK;
 }
 
+// Steady-state step of a producer that keeps several batches in flight: wait for an older slot
+// (wait_slot < 0: none) and submit a filled one, in a single boundary crossing.
+int cm_pipe_cycle(cm_pipe *p, int wait_slot, int submit_slot, float min_score, int want_centi) {
+    if (wait_slot >= 0)
+        if (int rc = cm_pipe_wait(p, wait_slot)) return rc;
+    return cm_pipe_submit(p, submit_slot, min_score, want_centi);
+}
+
 int cm_pipe_depth(cm_pipe *p) { return p ? (int)p->slots.size() : 0; }
 
 }  // extern "C"

@@ -200,3 +200,8 @@ class ScoringPipe:
 
     def wait(self, slot: int) -> None:
         check(self._lib.cm_pipe_wait(self._h, slot))
+
+    def cycle(self, wait_slot: int, submit_slot: int, min_score: float, want_centi: bool = False) -> None:
+        """``wait(wait_slot)`` (skipped when negative) then ``submit(submit_slot)`` in one call."""
+        check(self._lib.cm_pipe_cycle(self._h, wait_slot, submit_slot, ctypes.c_float(np.float32(min_score)),
+                                      1 if want_centi else 0))

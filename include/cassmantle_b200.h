@@ -148,6 +148,8 @@ int cm_pipe_buffers(cm_pipe *p, int slot, int n_guesses, int n_slots,
                     uint8_t **exact, float **scores, int32_t **centi);
 int cm_pipe_submit(cm_pipe *p, int slot, float min_score, int want_centi);
 int cm_pipe_wait(cm_pipe *p, int slot);
+/* cm_pipe_wait(wait_slot) (skipped when wait_slot < 0) followed by cm_pipe_submit(submit_slot). */
+int cm_pipe_cycle(cm_pipe *p, int wait_slot, int submit_slot, float min_score, int want_centi);
 
 /* ---- vocabulary lookup on the device -------------------------------- *
  * Replaces `inputs.lower()` (src/backend.py:304) + gensim's `key_to_index[word]` dict lookup

@@ -272,6 +272,17 @@ def test_pipe_matches_host_entry_point(small_engine):
     for s, (j, v) in inflight.items():
         pipe.wait(s)
         assert np.array_equal(v["scores"].view(np.uint32), want[j][0].view(np.uint32)), j
+    # cycle = wait(older slot) + submit(filled slot) in one call
+    idx, ln, _, slot, ex = synth.make_guess_batch(64, 2, 50_000, 3, seed=999)
+    w0 = small_engine.score_host(idx, ln, slot, ex, 0.01)[0]
+    for s in (0, 1):
+        v = pipe.buffers(s, 64, 2)
+        v["guess_idx"][:] = idx; v["guess_len"][:] = ln; v["answer_slot"][:] = slot; v["exact"][:] = ex
+    pipe.submit(0, 0.01)
+    pipe.cycle(0, 1, 0.01)
+    assert np.array_equal(pipe.buffers(0, 64, 2)["scores"].view(np.uint32), w0.view(np.uint32))
+    pipe.wait(1)
+    assert np.array_equal(pipe.buffers(1, 64, 2)["scores"].view(np.uint32), w0.view(np.uint32))
     with pytest.raises(CassMantleError):
         pipe.buffers(0, 4096, 16)              # beyond max_guesses
     with pytest.raises(CassMantleError):
