@@ -47,7 +47,7 @@ class ScoringEngine:
 
     @classmethod
     def from_vectors(cls, vectors: np.ndarray, device: int = 0,
-                     chunk_rows: int = 1 << 18) -> "ScoringEngine":
+                     chunk_rows: int = 1 << 20) -> "ScoringEngine":
         """Upload a host matrix (e.g. gensim's mmap'd ``wv.vectors``) chunk by chunk."""
         if vectors.ndim != 2 or vectors.dtype != np.float32:
             raise ValueError("vectors must be a 2-D float32 array")
