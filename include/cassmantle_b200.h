@@ -118,7 +118,8 @@ int cm_score_batch_device(cm_engine *e,
  * back and returns when `scores` (and `centi`, if not NULL) are valid.  This is what the
  * Python boundary (cassmantle_b200/backend.py) calls per micro-batch.  Page-locked
  * buffers (cudaHostAlloc / cudaHostRegister, e.g. torch pin_memory) are read and written
- * by the kernel directly; pageable ones go through one pinned staging block.             */
+ * by the kernel directly; pageable ones go through one pinned staging block.  `scores`
+ * and `centi` are overwritten while the call runs (also on error).                         */
 int cm_score_batch_host(cm_engine *e,
                         const int32_t *guess_idx, const int32_t *guess_len,
                         int n_guesses, int n_slots,
