@@ -277,9 +277,22 @@ def run_own(args) -> None:
 
     gather = None
     if world > 1 and args.collective == "fused":
+        # peer mappings need CUDA IPC between the ranks' processes; if any rank cannot set them up
+        # (a sandbox without IPC) every rank falls back to the NCCL all-gather and says so
         from cassmantle_b200.dist import ScoreGather
-        gather = ScoreGather(eng, B, depth=8)
-        gather.exchange_handles()
+        ok_local = 1.0
+        try:
+            gather = ScoreGather(eng, B, depth=8)
+            gather.exchange_handles()
+        except Exception as exc:      # noqa: BLE001
+            print(f"[bench] rank {rank}: peer-memory gather unavailable ({exc}); using NCCL", file=sys.stderr)
+            ok_local = 0.0
+        t_ok = torch.tensor([ok_local], device=dev)
+        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+        if t_ok.item() != 1.0:
+            if gather is not None:
+                gather.close()
+            gather = None
         dist.barrier()
 
     import ctypes
