@@ -46,7 +46,7 @@ N_ANSWERS = 2
 MIN_SCORE = 0.01
 RING = 64                      # distinct batches cycled through (64 x 79 MB of rows)
 OVERLAP = 1                    # CM_SCORE_OVERLAP_PREVIOUS: the ring's batches are independent
-PIPE_DEPTH = 4                 # batches in flight on the pipelined host path
+PIPE_DEPTH = 8                 # batches in flight on the pipelined host path
 BYTES_PER_GUESS = N * (D * 4 + 4) + 8      # N rows + N indices + len/slot + score
 METRIC = "guesses_scored_per_sec"
 UNIT = "guesses/s"
