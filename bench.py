@@ -514,11 +514,16 @@ def run_own(args) -> None:
                               (65536, 1, "configs[3] at one word per guess"),
                               (512, 8, "configs[1] micro-batch"),
                               (65536, 16, "configs[3] scale-out batch on one GPU"),
-                              (16384, 64, "configs[4] long-guess stress")]:
+                              (16384, 64, "configs[4] long-guess stress"),
+                              (4096, 16, "metric shape with Zipf(1.0) word frequencies instead of uniform rows")]:
             k_ring = 8
             bufs = []
             for i in range(k_ring):
                 idx2, ln2, _, slot2, ex2 = synth.make_guess_batch(b2, n2, V, N_ANSWERS, seed=7000 + i, near_frac=0.0)
+                if "Zipf" in tag:        # realistic traffic: rank r drawn with p ~ 1/r
+                    zr = np.random.default_rng(7100 + i)
+                    z = np.minimum(np.exp(zr.random(idx2.shape) * np.log(V)).astype(np.int64) - 1, V - 1)
+                    idx2 = np.where(idx2 >= 0, z, -1).astype(np.int32)
                 bufs.append([torch.from_numpy(a).to(dev) for a in (idx2, ln2, slot2, ex2)])
             out2 = torch.empty(b2, dtype=torch.float32, device=dev)
             ptr2 = [(q[0].data_ptr(), q[1].data_ptr(), q[2].data_ptr(), q[3].data_ptr()) for q in bufs]
