@@ -22,6 +22,7 @@ NVCC_FLAGS = [
     "-O3", "-std=c++17", "-lineinfo",
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-Xcompiler", "-fPIC,-O3,-Wall", "-shared", "-cudart", "static",
+    "--threads", "0",          # one compile job per .cu file
 ]
 
 
