@@ -418,25 +418,37 @@ def run_own(args) -> None:
         # ---- e2e: host buffers through the C ABI ---------------------------------------------
         # (a) pipelined: cm_pipe_* with PIPE_DEPTH batches in flight.  The ring's batches live in
         #     page-locked host memory (the pipe's slots, filled before the timed region); every
-        #     step DMAs that step's inputs to the GPU, scores them, and the step's scores land
-        #     back in page-locked host memory, where the host reads them.
+        #     step moves that step's inputs across PCIe to the GPU (at this batch size the scoring
+        #     kernel reads them from the slot itself; the copy-engine route is timed beside it),
+        #     scores them, and the step's scores land back in page-locked host memory, where the
+        #     host reads them.
         # (b) synchronous: one cm_score_batch_host call per step (what Backend.compute_scores uses).
         from cassmantle_b200.engine import ScoringPipe
-        if pipe is None:
-            pipe = ScoringPipe(eng, depth=RING, max_guesses=B, max_slots=N)
-            views = []
+        def make_pipe():
+            pp = ScoringPipe(eng, depth=RING, max_guesses=B, max_slots=N)
+            vv = []
             for s_i, (idx, ln, slot, ex) in enumerate(ring):
-                v = pipe.buffers(s_i, B, N)
+                v = pp.buffers(s_i, B, N)
                 v["guess_idx"][:] = idx
                 v["guess_len"][:] = ln
                 v["answer_slot"][:] = slot
                 v["exact"][:] = ex
-                views.append(v)
+                vv.append(v)
+            return pp, vv
+
+        if pipe is None:
+            pipe, views = make_pipe()
+            # the same pipe forced onto the copy engine (H2D DMA -> kernel -> D2H DMA), for comparison
+            os.environ["CM_PIPE_DIRECT_IN_MAX"] = os.environ["CM_PIPE_DIRECT_OUT_MAX"] = "0"
+            pipe_dma, views_dma = make_pipe()
+            del os.environ["CM_PIPE_DIRECT_IN_MAX"], os.environ["CM_PIPE_DIRECT_OUT_MAX"]
         submit, wait, cycle, ph = lib.cm_pipe_submit, lib.cm_pipe_wait, lib.cm_pipe_cycle, pipe._h
+        all_views = views
         checksum = 0.0
 
         def run_pipe(first: int, count: int, fill: bool = False) -> None:
             nonlocal checksum
+            views = all_views
             for i in range(first, first + count):
                 if not fill and i - first >= PIPE_DEPTH:               # steady state: one call per step
                     j = (i - PIPE_DEPTH) % RING
@@ -470,8 +482,23 @@ def run_own(args) -> None:
         e2e = {"value": args.steps * B * world / e2e_s, "unit": UNIT,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 4,
                "ms_per_step": e2e_s / args.steps * 1e3, "gpu_launches": e2e_launches,
-               "api": f"cm_pipe_cycle = cm_pipe_wait + cm_pipe_submit (C ABI), {PIPE_DEPTH} batches in flight, inputs DMA'd "
-                      f"from page-locked host slots, scores written back into them by the kernel"}
+               "api": f"cm_pipe_cycle = cm_pipe_wait + cm_pipe_submit (C ABI), {PIPE_DEPTH} batches in flight; at this batch "
+                      f"size the scoring kernel reads each step's inputs from the page-locked host slot across PCIe "
+                      f"and writes the scores back into it (no separate DMA)"}
+        # (a'') the same call forced onto the copy engine: H2D DMA -> kernel -> D2H DMA per step
+        ph, all_views = pipe_dma._h, views_dma
+        run_pipe(0, max(args.warmup, PIPE_DEPTH))
+        barrier()
+        t0 = time.perf_counter()
+        run_pipe(args.warmup, args.steps)
+        dma_s = max_over_ranks(time.perf_counter() - t0)
+        e2e["copy_engine_route"] = {"value": args.steps * B * world / dma_s, "unit": UNIT,
+                                    "ms_per_step": dma_s / args.steps * 1e3,
+                                    "note": "CM_PIPE_DIRECT_*_MAX=0: the route the pipe takes for batches above 8192 guesses"}
+        for j in range(2):
+            assert np.array_equal(np.asarray(views_dma[j]["scores"]).view(np.uint32),
+                                  np.asarray(views[j]["scores"]).view(np.uint32))
+        ph, all_views = pipe._h, views
         # (a') the same with the producer's copy into the slot inside the timed region
         n_fill = min(args.steps, 1000)
         run_pipe(0, PIPE_DEPTH, fill=True)

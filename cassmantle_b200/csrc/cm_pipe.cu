@@ -1,17 +1,20 @@
 // cassmantle_b200 -- pipelined host path (include/cassmantle_b200.h: cm_pipe_*).
 //
 // A pipe is a ring of `depth` slots.  Each slot owns a page-locked host block that the caller
-// fills in place (no staging copy), a device block the inputs are DMA'd into, a stream and an
-// event.  cm_pipe_submit() enqueues  H2D copy -> scoring kernel  on the slot's stream; the
-// kernel writes the scores straight back into the slot's page-locked block, so there is no
-// D2H copy to schedule.  With two or more slots the copy of batch i+1 runs on the copy engine
-// while batch i is being scored, and the host fills batch i+2.
+// fills in place (no staging copy), a device block of the same layout, a stream and an event.
+// cm_pipe_submit() enqueues ONE scoring kernel on the slot's stream for batches of ordinary size:
+// the kernel reads the batch from the page-locked block across PCIe and writes the scores back
+// into it, so there is no copy to schedule and the slots' kernels overlap on the GPU (the reads
+// of batch i+1 arrive while batch i is gathering).  Large batches go through the copy engine
+// instead (H2D of the inputs before the kernel, D2H of the scores after it): see the thresholds
+// below.  Either way the host fills batch i+2 meanwhile.
 //
 // This is the device-side half of the request micro-batcher that north_star places in
 // src/server.py (cassmantle_b200/server.py drives it); the reference has no counterpart.
 
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <new>
 #include <vector>
 
@@ -19,7 +22,7 @@
 
 struct cm_pipe_slot {
     unsigned char *h = nullptr;     // pinned: [idx | len | slot | exact | scores | centi]
-    unsigned char *d = nullptr;     // device: [idx | len | slot | exact]
+    unsigned char *d = nullptr;     // device: same layout (used by the DMA routes only)
     cudaStream_t stream = nullptr;
     cudaEvent_t done = nullptr;
     int n_guesses = 0, n_slots = 0;
@@ -32,6 +35,8 @@ struct cm_pipe {
     int max_guesses = 0, max_slots = 0;
     size_t slot_bytes = 0;
     std::vector<cm_pipe_slot> slots;
+    size_t direct_in_max = 0;       // inputs up to this many bytes are read in place by the kernel
+    int direct_out_max = 0;         // up to this many guesses the kernel writes scores in place
 };
 
 namespace {
@@ -46,6 +51,18 @@ void layout(cm_pipe_slot &s, size_t B, size_t N) {
     s.in_bytes = align_up(s.off_exact + B, 256);
     s.off_scores = s.in_bytes;
     s.off_centi = s.off_scores + align_up(B * 4, 16);
+}
+
+// Route thresholds (measured on B200, tools/probe_pipe.py).  Below them the
+// kernel reads the batch from / writes the scores to the page-locked block itself, which saves a
+// DMA enqueue per step and lets the PCIe reads of batch i+1 hide under the gather of batch i;
+// above them the copy engine moves whole blocks, which small PCIe transactions cannot match.
+constexpr size_t kDirectInMax = 640u << 10;   // bytes of packed inputs
+constexpr size_t kDirectOutMax = 8192;        // guesses; also caps the direct-input route
+
+size_t env_size(const char *name, size_t fallback) {
+    const char *v = getenv(name);
+    return v != nullptr && *v != 0 ? (size_t)strtoull(v, nullptr, 10) : fallback;
 }
 
 int check_slot(const cm_pipe *p, int slot) {
@@ -91,10 +108,12 @@ int cm_pipe_create(cm_pipe **out, cm_engine *e, int depth, int max_guesses, int 
     layout(probe, (size_t)max_guesses, (size_t)max_slots);
     p->slot_bytes = probe.off_centi + align_up((size_t)max_guesses * 4, 256);
     p->slots.resize(depth);
+    p->direct_in_max = env_size("CM_PIPE_DIRECT_IN_MAX", kDirectInMax);
+    p->direct_out_max = (int)env_size("CM_PIPE_DIRECT_OUT_MAX", kDirectOutMax);
     cm::DeviceGuard guard(e->device);
     for (auto &s : p->slots) {
         cudaError_t err = cudaHostAlloc(&s.h, p->slot_bytes, cudaHostAllocDefault);
-        if (err == cudaSuccess) err = cudaMalloc(&s.d, probe.in_bytes);
+        if (err == cudaSuccess) err = cudaMalloc(&s.d, p->slot_bytes);
         if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
         if (err == cudaSuccess) err = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming);
         if (err != cudaSuccess) {
@@ -139,12 +158,21 @@ int cm_pipe_submit(cm_pipe *p, int slot, float min_score, int want_centi) {
     if (s.in_flight) return fail(CM_ERR_STATE, "slot %d is already in flight", slot);
     cm_engine *e = p->engine;
     cm::DeviceGuard guard(e->device);
-    CM_CUDA(cudaMemcpyAsync(s.d, s.h, s.in_bytes, cudaMemcpyHostToDevice, s.stream));
-    if (int rc = cm::enqueue_score(e, (const int32_t *)s.d, (const int32_t *)(s.d + s.off_len),
-                                   s.n_guesses, s.n_slots, (const int32_t *)(s.d + s.off_slot),
-                                   s.d + s.off_exact, min_score, (float *)(s.h + s.off_scores),
-                                   want_centi ? (int32_t *)(s.h + s.off_centi) : nullptr, 0u, s.stream))
+    const bool direct_out = s.n_guesses <= p->direct_out_max;
+    const bool direct_in = direct_out && s.in_bytes <= p->direct_in_max;
+    const unsigned char *in = direct_in ? s.h : s.d;
+    unsigned char *res = direct_out ? s.h : s.d;
+    if (!direct_in) CM_CUDA(cudaMemcpyAsync(s.d, s.h, s.in_bytes, cudaMemcpyHostToDevice, s.stream));
+    if (int rc = cm::enqueue_score(e, (const int32_t *)in, (const int32_t *)(in + s.off_len),
+                                   s.n_guesses, s.n_slots, (const int32_t *)(in + s.off_slot),
+                                   in + s.off_exact, min_score, (float *)(res + s.off_scores),
+                                   want_centi ? (int32_t *)(res + s.off_centi) : nullptr, 0u, s.stream))
         return rc;
+    if (!direct_out) {
+        const size_t n = want_centi ? s.off_centi + (size_t)s.n_guesses * 4 - s.off_scores
+                                    : (size_t)s.n_guesses * 4;
+        CM_CUDA(cudaMemcpyAsync(s.h + s.off_scores, s.d + s.off_scores, n, cudaMemcpyDeviceToHost, s.stream));
+    }
     CM_CUDA(cudaEventRecord(s.done, s.stream));
     s.in_flight = true;
     return CM_OK;

@@ -238,11 +238,54 @@ def test_device_entry_point_in_a_cuda_graph(small_engine):
             assert np.array_equal(outs[i].cpu().numpy().view(np.uint32), wants[i].view(np.uint32)), (rep, i)
 
 
-def test_pipe_matches_host_entry_point(small_engine):
+PIPE_ROUTES = {"default": None, "copy-engine": ("0", "0"), "copy-in": ("0", "100000000"),
+               "in-place": ("100000000", "100000000")}
+
+
+def _pipe_route(monkeypatch, route):
+    """The pipe picks its route (kernel reads/writes the pinned block in place, or the copy
+    engine moves it) from the batch size; the thresholds are read at cm_pipe_create."""
+    if PIPE_ROUTES[route] is not None:
+        monkeypatch.setenv("CM_PIPE_DIRECT_IN_MAX", PIPE_ROUTES[route][0])
+        monkeypatch.setenv("CM_PIPE_DIRECT_OUT_MAX", PIPE_ROUTES[route][1])
+
+
+@pytest.mark.parametrize("route", list(PIPE_ROUTES))
+def test_pipe_slot_reuse_never_sees_a_previous_batch(small_engine, monkeypatch, route):
+    """One slot pair reused 40 times with a different batch each time: a kernel that reads the
+    page-locked block in place must see the bytes written since the previous launch."""
+    from cassmantle_b200.engine import ScoringPipe
+    _pipe_route(monkeypatch, route)
+    small_engine.set_answers(np.array([11, 222, 3333], np.int32))
+    small_engine.synchronize()
+    pipe = ScoringPipe(small_engine, depth=2, max_guesses=1024, max_slots=4)
+    want = {}
+    for i in range(40):
+        s = i % 2
+        if i >= 2:
+            pipe.wait(s)
+            got = pipe.buffers(s, 1024, 4)
+            assert np.array_equal(got["scores"].view(np.uint32), want[i - 2][0].view(np.uint32)), i - 2
+            assert np.array_equal(got["centi"], want[i - 2][1]), i - 2
+        idx, ln, _, slot, ex = synth.make_guess_batch(1024, 4, 50_000, 3, seed=7000 + i, ragged=True)
+        want[i] = small_engine.score_host(idx, ln, slot, ex, 0.01, want_centi=True)
+        v = pipe.buffers(s, 1024, 4)
+        v["guess_idx"][:] = idx; v["guess_len"][:] = ln; v["answer_slot"][:] = slot; v["exact"][:] = ex
+        v["scores"][:] = -1.0
+        pipe.submit(s, 0.01, want_centi=True)
+    for i in (38, 39):
+        pipe.wait(i % 2)
+        assert np.array_equal(pipe.buffers(i % 2, 1024, 4)["scores"].view(np.uint32), want[i][0].view(np.uint32))
+    pipe.close()
+
+
+@pytest.mark.parametrize("route", list(PIPE_ROUTES))
+def test_pipe_matches_host_entry_point(small_engine, monkeypatch, route):
     """cm_pipe_*: slots filled in place, several in flight, results bit-identical to the
     synchronous host call; shapes may differ from slot to slot and slots are reusable."""
     from cassmantle_b200._lib import CassMantleError
     from cassmantle_b200.engine import ScoringPipe
+    _pipe_route(monkeypatch, route)
     ans = np.array([7, 4242, 31337], np.int32)
     small_engine.set_answers(ans)
     small_engine.synchronize()
