@@ -8,7 +8,8 @@ V = synth.FULL_ROWS
 lib = _lib.load()
 eng = ScoringEngine.synthetic(V, 300, 0, 0)
 ms32 = ctypes.c_float(np.float32(0.01))
-for B, N in [(4096, 16), (512, 8), (4096, 1), (64, 1), (65536, 16)]:
+SHAPES = [tuple(int(x) for x in a.split('x')) for a in sys.argv[1:]] or [(4096, 16), (512, 8), (4096, 1), (64, 1), (65536, 16)]
+for B, N in SHAPES:
     idx, ln, ans, slot, ex = synth.make_guess_batch(B, N, V, 2, seed=1, near_frac=0.0)
     eng.set_answers(ans)
     ref = None
