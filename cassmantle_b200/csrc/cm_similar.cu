@@ -10,17 +10,22 @@
 // no tensor-core work either (a BATCH of queries would make it a skinny GEMM; not built).
 //
 //   cm_row_norm_kernel   once per engine: norms[V]
-//   cm_dist_kernel       dists[r] = dot(row r, mean) / norms[r]; 4 rows per warp in flight
-//   cm_hist_kernel x4    radix select of the k-th largest key, 8 bits per pass, over the
-//                        12 MB of dists (L2-resident); each pass re-derives the prefix chosen
-//                        by the previous one from its histogram, so there is no host round trip
-//   cm_collect_kernel    everything above the threshold + ties until k candidates
-//   cm_sort_kernel       bitonic sort of the <= 1024 candidates, (dist desc, row asc)
+//   cm_query_kernel      mean (one warp)
+//   cm_scan_kernel       dists[r] = dot(row r, mean) / norms[r], and counts every distance into
+//                        a 16-bit-prefix histogram on the way
+//   cm_pick_kernel       finds the bin of the k-th largest distance from the histograms, collects
+//                        that bin and everything above it; the last CTA sorts (dist desc, row asc)
+// A query whose k-th distance shares its bin with thousands of others (duplicated rows) is
+// finished by the exact radix select instead: cm_hist_kernel x4 (8 bits per pass over the 12 MB
+// of dists, each pass re-deriving the previous one's prefix on the device), cm_collect_kernel,
+// cm_sort_kernel.
 //
 // NaN distances (NaN rows, zero norms) rank last, as numpy's argsort places them.
 
 #include <cuda_runtime.h>
 
+#include <cstdlib>
+#include <cstring>
 #include <new>
 
 #include "cm_common.cuh"
@@ -76,10 +81,50 @@ __global__ void cm_query_kernel(const float *__restrict__ table, int dim, int32_
     }
 }
 
-template <int VPL>
-__global__ void __launch_bounds__(256)
-cm_dist_kernel(const float *__restrict__ table, int64_t n_rows, int dim4, const float *__restrict__ mean,
-               const float *__restrict__ norms, float *__restrict__ dists) {
+// ---- fast path: scan and select in three launches --------------------------------------
+// The scan already holds every distance in a register once, so it also counts them: a
+// 65536-bin histogram of the top 16 key bits (one fire-and-forget global add per row; the bins
+// around zero are the busiest and still see only one add per ~60 ns) and, through shared
+// memory, the 256-bin histogram of the top 8 bits.  cm_pick_kernel then finds the 16-bit bin
+// holding the k-th largest key from 2 x 256 counters, takes everything above it plus that one
+// bin's population (a few dozen rows: the bin is 1/128 of its value wide), and the last CTA to
+// finish sorts them.  If that bin is too crowded to sort in one CTA (thousands of equal
+// distances: duplicated rows) the call falls back to the 4-pass radix select below.
+constexpr int kBucketCap = 3072;                       // + kMaxTopK = 4096 sortable entries
+
+struct PickState {
+    unsigned hist8[256];
+    unsigned n_above, n_bucket, ticket, pad;
+    unsigned hist16[65536];
+};
+
+// dist = dot / norm for one row: store it and count its key
+__device__ __forceinline__ void emit_dist(int64_t row, float dot, float norm, float *__restrict__ dists,
+                                          unsigned *__restrict__ hist16, unsigned *sh_hist8) {
+    const float d = dot / norm;
+    dists[row] = d;
+    const uint32_t key = key_of(d);
+    atomicAdd(&hist16[key >> 16], 1u);
+    atomicAdd(&sh_hist8[key >> 24], 1u);
+}
+
+// The scan: dists[r] = dot(row r, mean) / norms[r] for every row, one row per warp-wide load
+// (lane + 32 v), kRowsPerWarp consecutive rows per warp per round, rounds interleaved across the
+// whole grid.  Loads and FMAs are written row by row on purpose: the compiler then requests a
+// row, reduces it while the next rows' requests go out, and never holds more than a few
+// registers per row.  Measured alternatives (B200, 3M x 300, whole query):
+// all rows of the round buffered first 685-720 us; 16 lanes per row with two register buffers
+// in flight 702 us; one row per round at full occupancy 750-764 us; contiguous slices per CTA
+// handed out dynamically 654 us; this form 620-635 us.
+template <int VPL, int MIN_BLOCKS>
+__global__ void __launch_bounds__(256, MIN_BLOCKS)
+cm_scan_kernel(const float *__restrict__ table, int64_t n_rows, int dim4, const float *__restrict__ mean,
+               const float *__restrict__ norms, float *__restrict__ dists, PickState *__restrict__ ps) {
+    __shared__ unsigned sh_hist8[256];
+    sh_hist8[threadIdx.x] = 0;
+    __syncthreads();
+    cm::pdl_launch_dependents();
+    cm::pdl_wait();                                     // the query kernel wrote `mean`
     const int lane = threadIdx.x & 31;
     const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t n_warps = (int64_t)gridDim.x * (blockDim.x >> 5);
@@ -91,25 +136,19 @@ cm_dist_kernel(const float *__restrict__ table, int64_t n_rows, int dim4, const 
         q[v] = j < dim4 ? reinterpret_cast<const float4 *>(mean)[j] : make_float4(0.f, 0.f, 0.f, 0.f);
     }
     for (int64_t r0 = warp * kRowsPerWarp; r0 < n_rows; r0 += n_warps * kRowsPerWarp) {
-        float4 buf[kRowsPerWarp][VPL];
-#pragma unroll
-        for (int i = 0; i < kRowsPerWarp; ++i) {
-            const int64_t r = r0 + i;
-#pragma unroll
-            for (int v = 0; v < VPL; ++v) {
-                const int j = lane + 32 * v;
-                buf[i][v] = (r < n_rows && j < dim4) ? cm::ld_stream_f4(t4 + r * dim4 + j)
-                                                     : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-        }
         float p[kRowsPerWarp];
 #pragma unroll
         for (int i = 0; i < kRowsPerWarp; ++i) {
+            const int64_t r = r0 + i;
             float s = 0.f;
 #pragma unroll
             for (int v = 0; v < VPL; ++v) {
-                s = fmaf(buf[i][v].x, q[v].x, s); s = fmaf(buf[i][v].y, q[v].y, s);
-                s = fmaf(buf[i][v].z, q[v].z, s); s = fmaf(buf[i][v].w, q[v].w, s);
+                const int j = lane + 32 * v;
+                if (r < n_rows && j < dim4) {
+                    const float4 x = cm::ld_stream_f4(t4 + r * dim4 + j);
+                    s = fmaf(x.x, q[v].x, s); s = fmaf(x.y, q[v].y, s);
+                    s = fmaf(x.z, q[v].z, s); s = fmaf(x.w, q[v].w, s);
+                }
             }
             p[i] = s;
         }
@@ -122,9 +161,133 @@ cm_dist_kernel(const float *__restrict__ table, int64_t n_rows, int dim4, const 
             float mine = p[0];
 #pragma unroll
             for (int i = 1; i < kRowsPerWarp; ++i) mine = (lane == i) ? p[i] : mine;
-            dists[r0 + lane] = mine / norms[r0 + lane];
+            emit_dist(r0 + lane, mine, norms[r0 + lane], dists, ps->hist16, sh_hist8);
         }
     }
+    __syncthreads();
+    if (sh_hist8[threadIdx.x]) atomicAdd(&ps->hist8[threadIdx.x], sh_hist8[threadIdx.x]);
+}
+
+// Which of 256 bins, scanned from bin 255 downwards, holds the k-th entry; *above = entries in
+// the bins before it.  Called by one full warp; every lane returns the same answer.
+__device__ int find_bin_from_top(const unsigned *h, unsigned k, unsigned *above) {
+    const int lane = threadIdx.x & 31;
+    const int first = 255 - 8 * lane;                   // this lane's bins: first, first-1, ..., first-7
+    unsigned mine = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) mine += h[first - i];
+    unsigned incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned up = __shfl_up_sync(cm::kFullMask, incl, o);
+        if (lane >= o) incl += up;
+    }
+    const unsigned reached = __ballot_sync(cm::kFullMask, incl >= k);
+    const int owner = reached ? __ffs(reached) - 1 : 31;
+    unsigned acc = incl - mine;
+    int bin = first - 7;
+    for (int i = 0; i < 8; ++i) {
+        const unsigned c = h[first - i];
+        if (acc + c >= k) { bin = first - i; break; }
+        if (i < 7) acc += c;
+    }
+    *above = __shfl_sync(cm::kFullMask, acc, owner);
+    return __shfl_sync(cm::kFullMask, bin, owner);
+}
+
+// Collect everything in or above the 16-bit bin of the k-th largest key; the last CTA to finish
+// sorts the candidates by (distance desc, row asc), writes the first k and clears the counters
+// for the next query.  *n_out = k, or -1 when the bin holds more than bucket_cap (<= kBucketCap) rows.
+__global__ void __launch_bounds__(256)
+cm_pick_kernel(const float *__restrict__ dists, int64_t n, PickState *ps, unsigned k, unsigned bucket_cap,
+               unsigned long long *cand, int32_t *__restrict__ rows_out, float *__restrict__ sims_out,
+               int *__restrict__ n_out) {
+    __shared__ unsigned long long s[kMaxTopK + kBucketCap];
+    __shared__ unsigned sh[256];
+    __shared__ unsigned s_bin, s_above, s_pop;
+    __shared__ bool s_last;
+    const unsigned t = threadIdx.x;
+    cm::pdl_wait();                                     // the scan has finished and its counts are visible
+    sh[t] = __ldcg(&ps->hist8[t]);
+    __syncthreads();
+    if (t < 32) {
+        unsigned above;
+        const int c = find_bin_from_top(sh, k, &above);
+        if (t == 0) { s_bin = (unsigned)c; s_above = above; }
+    }
+    __syncthreads();
+    const unsigned coarse = s_bin, above_coarse = s_above;
+    __syncthreads();
+    sh[t] = __ldcg(&ps->hist16[coarse * 256 + t]);
+    __syncthreads();
+    if (t < 32) {
+        unsigned above;
+        const int f = find_bin_from_top(sh, k - above_coarse, &above);
+        if (t == 0) { s_bin = coarse * 256 + (unsigned)f; s_above = above_coarse + above; s_pop = sh[f]; }
+    }
+    __syncthreads();
+    const uint32_t bin = s_bin;                         // top 16 key bits of the k-th largest distance
+    const unsigned total = s_above + s_pop;             // rows in or above that bin: >= k
+    const bool crowded = s_pop > bucket_cap;
+    if (!crowded) {
+        const int64_t n4 = n >> 2;
+        const float4 *d4 = reinterpret_cast<const float4 *>(dists);
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + t; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+            const float4 v = d4[i];
+            const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const uint32_t key = key_of(e[c]);
+                if ((key >> 16) >= bin) {
+                    const unsigned slot = atomicAdd(&ps->n_above, 1u);
+                    cand[slot] = ((unsigned long long)(~key) << 32) | (uint32_t)(4 * i + c);
+                }
+            }
+        }
+        if (blockIdx.x == 0 && t < (unsigned)(n & 3)) {
+            const int64_t i = (n4 << 2) + t;
+            const uint32_t key = key_of(dists[i]);
+            if ((key >> 16) >= bin) {
+                const unsigned slot = atomicAdd(&ps->n_above, 1u);
+                cand[slot] = ((unsigned long long)(~key) << 32) | (uint32_t)i;
+            }
+        }
+    }
+    __threadfence();
+    __syncthreads();
+    if (t == 0) s_last = atomicAdd(&ps->ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (crowded) {
+        if (t == 0) *n_out = -1;
+    } else {
+        unsigned size = 64;
+        while (size < total) size <<= 1;
+        for (unsigned i = t; i < size; i += blockDim.x) s[i] = i < total ? __ldcg(&cand[i]) : ~0ull;
+        __syncthreads();
+        for (unsigned span = 2; span <= size; span <<= 1) {         // bitonic, ascending = best first
+            for (unsigned stride = span >> 1; stride > 0; stride >>= 1) {
+                for (unsigned c = t; c < size / 2; c += blockDim.x) {
+                    const unsigned lo = 2 * c - (c & (stride - 1));      // c-th pair of this stride
+                    const unsigned hi = lo + stride;
+                    const bool up = (lo & span) == 0;
+                    const unsigned long long a = s[lo], b = s[hi];
+                    if ((a > b) == up) { s[lo] = b; s[hi] = a; }
+                }
+                __syncthreads();
+            }
+        }
+        for (unsigned i = t; i < k; i += blockDim.x) {
+            const int32_t r = (int32_t)(s[i] & 0xffffffffull);
+            rows_out[i] = r;
+            sims_out[i] = dists[r];
+        }
+        if (t == 0) *n_out = (int)k;
+    }
+    // leave the counters clear for the next query
+    unsigned *w = reinterpret_cast<unsigned *>(ps);
+    for (unsigned i = t; i < sizeof(PickState) / sizeof(unsigned); i += blockDim.x) w[i] = 0u;
 }
 
 // Radix-select state: hist[pass][256]; the prefix chosen so far is re-derived by every CTA.
@@ -246,6 +409,9 @@ struct cm_similar_state {
     int32_t *d_rows_out = nullptr;
     float *d_sims_out = nullptr;
     int *d_n_out = nullptr;
+    PickState *d_pick = nullptr;
+    unsigned char *h_result = nullptr;   // page-locked: rows[kMaxTopK] | sims[kMaxTopK] | n -- the kernels write it directly
+    unsigned long long *d_cand = nullptr;
     bool norms_ready = false;
 };
 
@@ -255,9 +421,10 @@ void similar_state_free(cm_engine *e) {
     cm_similar_state *s = e->similar;
     if (s == nullptr) return;
     void *ptrs[] = {s->d_norms, s->d_mean, s->d_dists, s->d_sel, s->d_cand_key, s->d_cand_row,
-                    s->d_rows_out, s->d_sims_out, s->d_n_out};
+                    s->d_rows_out, s->d_sims_out, s->d_n_out, s->d_pick, s->d_cand};
     for (void *p : ptrs)
         if (p) cudaFree(p);
+    if (s->h_result) cudaFreeHost(s->h_result);
     delete s;
     e->similar = nullptr;
 }
@@ -278,6 +445,10 @@ static int similar_state(cm_engine *e, cm_similar_state **out) {
         if (err == cudaSuccess) err = cudaMalloc(&s->d_rows_out, kMaxTopK * sizeof(int32_t));
         if (err == cudaSuccess) err = cudaMalloc(&s->d_sims_out, kMaxTopK * sizeof(float));
         if (err == cudaSuccess) err = cudaMalloc(&s->d_n_out, sizeof(int));
+        if (err == cudaSuccess) err = cudaMalloc(&s->d_pick, sizeof(PickState));
+        if (err == cudaSuccess) err = cudaMalloc(&s->d_cand, (kMaxTopK + kBucketCap) * sizeof(unsigned long long));
+        if (err == cudaSuccess) err = cudaMemset(s->d_pick, 0, sizeof(PickState));
+        if (err == cudaSuccess) err = cudaHostAlloc(&s->h_result, kMaxTopK * 8 + 16, cudaHostAllocDefault);
         if (err != cudaSuccess) {
             cudaGetLastError();
             cm::similar_state_free(e);
@@ -301,23 +472,66 @@ extern "C" int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_o
     if (int rc = similar_state(e, &s)) return rc;
     cudaStream_t st = e->stream;
     const int dim4 = e->dim / 4;
-    const int grid = 148 * 8;
+    const int grid = 148 * 8;                                        // row norms, once
     if (!s->norms_ready) {                                           // gensim fill_norms(), once
         cm_row_norm_kernel<<<grid, 256, 0, st>>>(e->d_table, e->n_rows, dim4, s->d_norms);
         cm::count_launch();
         s->norms_ready = true;
     }
+    const unsigned kk = (unsigned)((int64_t)k < e->n_rows ? k : e->n_rows);
     cm_query_kernel<<<1, 32, 0, st>>>(e->d_table, e->dim, row, s->d_norms, s->d_mean);
     cm::count_launch();
+    // scan + pick ride on programmatic dependent launches: each starts its prologue while the
+    // previous kernel drains and waits (griddepcontrol.wait) before it touches that kernel's output
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.stream = st;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    // test hook: a smaller cap (0 = always) sends queries down the radix-select fallback
+    static const unsigned bucket_cap = [] {
+        const char *v = getenv("CM_SIMILAR_BUCKET_CAP");
+        const long c = v != nullptr && *v != 0 ? atol(v) : (long)kBucketCap;
+        return (unsigned)(c < 0 ? 0 : (c > kBucketCap ? kBucketCap : c));
+    }();
+    const float *table = e->d_table, *mean = s->d_mean, *norms = s->d_norms;
+    cfg.blockDim = dim3(256);
+#define CM_CASE(V, MB)                                                                             \
+    case V:                                                                                        \
+        cfg.gridDim = dim3(148 * MB);                                                              \
+        cudaLaunchKernelEx(&cfg, cm_scan_kernel<V, MB>, table, e->n_rows, dim4, mean, norms, s->d_dists, s->d_pick); \
+        break;
     switch ((dim4 + 31) / 32) {
-#define CM_CASE(V) case V: cm_dist_kernel<V><<<grid, 256, 0, st>>>(e->d_table, e->n_rows, dim4, s->d_mean, s->d_norms, s->d_dists); break;
-        CM_CASE(1) CM_CASE(2) CM_CASE(3) CM_CASE(4) CM_CASE(5) CM_CASE(6) CM_CASE(7)
-        default: cm_dist_kernel<8><<<grid, 256, 0, st>>>(e->d_table, e->n_rows, dim4, s->d_mean, s->d_norms, s->d_dists); break;
-#undef CM_CASE
+        CM_CASE(1, 3) CM_CASE(2, 3) CM_CASE(3, 3) CM_CASE(4, 2) CM_CASE(5, 2) CM_CASE(6, 2) CM_CASE(7, 2)
+        default:
+            cfg.gridDim = dim3(148 * 2);
+            cudaLaunchKernelEx(&cfg, cm_scan_kernel<8, 2>, table, e->n_rows, dim4, mean, norms, s->d_dists, s->d_pick);
+            break;
     }
+#undef CM_CASE
     cm::count_launch();
+    cfg.gridDim = dim3(148 * 4);
+    cfg.blockDim = dim3(256);
+    // the pick kernel writes the result straight into page-locked host memory: no copies to enqueue
+    int32_t *h_rows = reinterpret_cast<int32_t *>(s->h_result);
+    float *h_sims = reinterpret_cast<float *>(s->h_result + kMaxTopK * 4);
+    int *h_n = reinterpret_cast<int *>(s->h_result + kMaxTopK * 8);
+    cudaLaunchKernelEx(&cfg, cm_pick_kernel, (const float *)s->d_dists, e->n_rows, s->d_pick,
+                       kk, bucket_cap, s->d_cand, h_rows, h_sims, h_n);
+    cm::count_launch();
+    CM_CUDA(cudaGetLastError());
+    CM_CUDA(cudaStreamSynchronize(st));
+    if (*h_n >= 0) {
+        memcpy(rows_out, h_rows, kk * sizeof(int32_t));
+        memcpy(sims_out, h_sims, kk * sizeof(float));
+        *n_out = *h_n;
+        return CM_OK;
+    }
+    // The k-th distance sits in a 16-bit bin with thousands of rows (duplicates): exact 4-pass
+    // radix select over the distances the scan left behind.
     CM_CUDA(cudaMemsetAsync(s->d_sel, 0, sizeof(SelectState), st));
-    const unsigned kk = (unsigned)((int64_t)k < e->n_rows ? k : e->n_rows);
     for (int pass = 0; pass < 4; ++pass) {
         cm_hist_kernel<<<148 * 4, 256, 0, st>>>(s->d_dists, e->n_rows, s->d_sel, pass, kk);
         cm::count_launch();

@@ -84,3 +84,58 @@ def test_full_size_most_similar():
             assert abs(float(s) - float(O.similarity(np.stack([qv, v]), 0, 1))) <= 2 * COS_TOL
         again, sims2 = eng.most_similar(q, 51)
         assert np.array_equal(rows, again) and np.array_equal(sims, sims2)
+
+
+def test_most_similar_crowded_bin_takes_the_radix_fallback():
+    """Thousands of rows with the same distance around the k-th place (duplicated rows): the
+    fast path's one-bin sort cannot hold them, the call must fall back and still be exact."""
+    from cassmantle_b200.engine import ScoringEngine
+    rng = np.random.default_rng(11)
+    vec = rng.standard_normal((20_000, 300), dtype=np.float32)
+    vec[1000:6000] = vec[1000] * rng.uniform(0.5, 2.0, (5000, 1)).astype(np.float32)   # 5000 rows, cosine 1 with row 1000
+    with ScoringEngine.from_vectors(vec) as eng:
+        dists = O.most_similar_dists(vec, 1000)
+        for k in (10, 1024):
+            rows, sims = eng.most_similar(1000, k)
+            assert len(set(rows.tolist())) == k and np.all((rows >= 1000) & (rows < 6000))
+            assert np.all(np.abs(sims - dists[rows]) <= COS_TOL) and np.all(np.diff(sims) <= 0)
+        # and the fast path is clean again afterwards (its counters were reset by the fallback call)
+        d2 = O.most_similar_dists(vec, 7)
+        rows, sims = eng.most_similar(7, 40)
+        _check(rows, sims, d2, 40, 7)
+
+
+@pytest.mark.parametrize("cap", ["0", "5"])
+def test_most_similar_forced_fallback_matches_fast_path(small_table, cap):
+    """CM_SIMILAR_BUCKET_CAP (read once per process) is a test hook, so this runs in a child."""
+    import os, subprocess, sys, textwrap
+    code = textwrap.dedent("""
+        import numpy as np
+        from cassmantle_b200 import synth
+        from cassmantle_b200.engine import ScoringEngine
+        with ScoringEngine.synthetic(50_000, 300, seed=3) as eng:
+            for q, k in ((5, 1), (77, 51), (4242, 1024)):
+                r, s = eng.most_similar(q, k)
+                print(q, k, int(np.bitwise_xor.reduce(r.astype(np.int64) * 2654435761 % (1 << 31))), float(s.sum()))
+    """)
+    outs = []
+    for env_cap in (None, cap):
+        env = dict(os.environ)
+        env.pop("CM_SIMILAR_BUCKET_CAP", None)
+        if env_cap is not None:
+            env["CM_SIMILAR_BUCKET_CAP"] = env_cap
+        outs.append(subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True,
+                                   cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))), check=True).stdout)
+    assert outs[0] == outs[1] and len(outs[0].splitlines()) == 3
+
+
+@pytest.mark.parametrize("dim", [64, 128, 512, 1024])
+def test_most_similar_other_dimensions(dim):
+    """Dimensions other than 300 take the generic scan kernel; same selection after it."""
+    from cassmantle_b200.engine import ScoringEngine
+    rng = np.random.default_rng(dim)
+    vec = rng.standard_normal((3001, dim), dtype=np.float32)
+    with ScoringEngine.from_vectors(vec) as eng:
+        for q, k in ((0, 5), (3000, 100)):
+            rows, sims = eng.most_similar(q, k)
+            _check(rows, sims, O.most_similar_dists(vec, q), k, q)
