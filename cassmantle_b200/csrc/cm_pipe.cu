@@ -14,7 +14,9 @@
 
 #include <cuda_runtime.h>
 
+#include <chrono>
 #include <cstdlib>
+#include <cstring>
 #include <new>
 #include <vector>
 
@@ -37,6 +39,14 @@ struct cm_pipe {
     std::vector<cm_pipe_slot> slots;
     size_t direct_in_max = 0;       // inputs up to this many bytes are read in place by the kernel
     int direct_out_max = 0;         // up to this many guesses the kernel writes scores in place
+    // Mid-size batches (kSmallIn < inputs <= direct_in_max): which route is faster depends on how
+    // busy the PCIe path is, so the pipe times both and keeps the better one (see pick_route).
+    enum Route { kAuto, kInPlace, kCopy } route = kAuto;
+    enum Phase { kWarm, kTryInPlace, kTryCopy, kHold } phase = kWarm;
+    int phase_submits = 0;
+    bool best_in_place = true;
+    std::chrono::steady_clock::time_point window_start;
+    double window_s[2] = {0.0, 0.0};          // [in place, copy engine] seconds per timed window
 };
 
 namespace {
@@ -59,6 +69,47 @@ void layout(cm_pipe_slot &s, size_t B, size_t N) {
 // above them the copy engine moves whole blocks, which small PCIe transactions cannot match.
 constexpr size_t kDirectInMax = 640u << 10;   // bytes of packed inputs
 constexpr size_t kDirectOutMax = 8192;        // guesses; also caps the direct-input route
+
+// Up to this many input bytes a step is bound by launch/enqueue cost, not by PCIe: always in place.
+constexpr size_t kSmallIn = 64u << 10;
+// Route tuning for mid-size batches: skip the start-up, then time kWindow submits on each route
+// (after kSettle submits, so that batches submitted on the other route have drained), keep the
+// winner for kHold submits, and try again.  The copy engine has to win by 3 % to be chosen: when
+// the producer is the bottleneck both windows measure the producer, and in place costs the host
+// one call per step instead of three.
+constexpr int kWarmSubmits = 64, kSettle = 32, kWindow = 256, kHold = 16384;
+
+// true: this mid-size batch goes in place; false: through the copy engine
+bool pick_route(cm_pipe *p) {
+    if (p->route != cm_pipe::kAuto) return p->route == cm_pipe::kInPlace;
+    const int n = ++p->phase_submits;
+    switch (p->phase) {
+        case cm_pipe::kWarm:
+            if (n >= kWarmSubmits) { p->phase = cm_pipe::kTryInPlace; p->phase_submits = 0; }
+            return true;
+        case cm_pipe::kTryInPlace:
+        case cm_pipe::kTryCopy: {
+            const bool in_place = p->phase == cm_pipe::kTryInPlace;
+            if (n == kSettle) p->window_start = std::chrono::steady_clock::now();
+            if (n == kSettle + kWindow) {
+                p->window_s[in_place ? 0 : 1] =
+                    std::chrono::duration<double>(std::chrono::steady_clock::now() - p->window_start).count();
+                p->phase_submits = 0;
+                if (in_place) {
+                    p->phase = cm_pipe::kTryCopy;
+                } else {
+                    p->best_in_place = !(p->window_s[1] < 0.97 * p->window_s[0]);
+                    p->phase = cm_pipe::kHold;
+                }
+            }
+            return in_place;
+        }
+        case cm_pipe::kHold:
+            if (n >= kHold) { p->phase = cm_pipe::kTryInPlace; p->phase_submits = 0; }
+            return p->best_in_place;
+    }
+    return true;
+}
 
 size_t env_size(const char *name, size_t fallback) {
     const char *v = getenv(name);
@@ -110,6 +161,10 @@ int cm_pipe_create(cm_pipe **out, cm_engine *e, int depth, int max_guesses, int 
     p->slots.resize(depth);
     p->direct_in_max = env_size("CM_PIPE_DIRECT_IN_MAX", kDirectInMax);
     p->direct_out_max = (int)env_size("CM_PIPE_DIRECT_OUT_MAX", kDirectOutMax);
+    if (const char *r = getenv("CM_PIPE_ROUTE")) {          // "inplace" | "copy" pin the mid-size route
+        if (strcmp(r, "inplace") == 0) p->route = cm_pipe::kInPlace;
+        else if (strcmp(r, "copy") == 0) p->route = cm_pipe::kCopy;
+    }
     cm::DeviceGuard guard(e->device);
     for (auto &s : p->slots) {
         cudaError_t err = cudaHostAlloc(&s.h, p->slot_bytes, cudaHostAllocDefault);
@@ -158,8 +213,9 @@ int cm_pipe_submit(cm_pipe *p, int slot, float min_score, int want_centi) {
     if (s.in_flight) return fail(CM_ERR_STATE, "slot %d is already in flight", slot);
     cm_engine *e = p->engine;
     cm::DeviceGuard guard(e->device);
-    const bool direct_out = s.n_guesses <= p->direct_out_max;
-    const bool direct_in = direct_out && s.in_bytes <= p->direct_in_max;
+    bool direct_out = s.n_guesses <= p->direct_out_max;
+    bool direct_in = direct_out && s.in_bytes <= p->direct_in_max;
+    if (direct_in && s.in_bytes > kSmallIn && !pick_route(p)) direct_in = direct_out = false;
     const unsigned char *in = direct_in ? s.h : s.d;
     unsigned char *res = direct_out ? s.h : s.d;
     if (!direct_in) CM_CUDA(cudaMemcpyAsync(s.d, s.h, s.in_bytes, cudaMemcpyHostToDevice, s.stream));

@@ -238,16 +238,19 @@ def test_device_entry_point_in_a_cuda_graph(small_engine):
             assert np.array_equal(outs[i].cpu().numpy().view(np.uint32), wants[i].view(np.uint32)), (rep, i)
 
 
-PIPE_ROUTES = {"default": None, "copy-engine": ("0", "0"), "copy-in": ("0", "100000000"),
-               "in-place": ("100000000", "100000000")}
+PIPE_ROUTES = {"default": None, "copy-engine": ("0", "0", None), "copy-in": ("0", "100000000", None),
+               "in-place": ("100000000", "100000000", "inplace"), "mid-size-by-copy": (None, None, "copy")}
 
 
 def _pipe_route(monkeypatch, route):
     """The pipe picks its route (kernel reads/writes the pinned block in place, or the copy
     engine moves it) from the batch size; the thresholds are read at cm_pipe_create."""
+    for name in ("CM_PIPE_DIRECT_IN_MAX", "CM_PIPE_DIRECT_OUT_MAX", "CM_PIPE_ROUTE"):
+        monkeypatch.delenv(name, raising=False)
     if PIPE_ROUTES[route] is not None:
-        monkeypatch.setenv("CM_PIPE_DIRECT_IN_MAX", PIPE_ROUTES[route][0])
-        monkeypatch.setenv("CM_PIPE_DIRECT_OUT_MAX", PIPE_ROUTES[route][1])
+        for name, v in zip(("CM_PIPE_DIRECT_IN_MAX", "CM_PIPE_DIRECT_OUT_MAX", "CM_PIPE_ROUTE"), PIPE_ROUTES[route]):
+            if v is not None:
+                monkeypatch.setenv(name, v)
 
 
 @pytest.mark.parametrize("route", list(PIPE_ROUTES))
@@ -276,6 +279,41 @@ def test_pipe_slot_reuse_never_sees_a_previous_batch(small_engine, monkeypatch, 
     for i in (38, 39):
         pipe.wait(i % 2)
         assert np.array_equal(pipe.buffers(i % 2, 1024, 4)["scores"].view(np.uint32), want[i][0].view(np.uint32))
+    pipe.close()
+
+
+def test_pipe_route_tuning_keeps_results_identical(small_engine, monkeypatch):
+    """Mid-size batches (64 KiB < inputs <= 640 KiB): the pipe times the in-place route against the
+    copy engine and switches between them as it runs.  1400 submits walk through every phase
+    (start-up, both trial windows, hold); each result must equal the blocking call's."""
+    from cassmantle_b200.engine import ScoringPipe
+    _pipe_route(monkeypatch, "default")
+    small_engine.set_answers(np.array([5, 50, 500], np.int32))
+    small_engine.synchronize()
+    B, N, depth, n_batches = 2048, 16, 4, 6
+    batches, want = [], []
+    for i in range(n_batches):
+        idx, ln, _, slot, ex = synth.make_guess_batch(B, N, 50_000, 3, seed=8100 + i, ragged=True)
+        batches.append((idx, ln, slot, ex))
+        want.append(small_engine.score_host(idx, ln, slot, ex, 0.01)[0])
+    pipe = ScoringPipe(small_engine, depth=depth, max_guesses=B, max_slots=N)
+    which = {}
+    for i in range(1400):
+        s = i % depth
+        if i >= depth:
+            pipe.wait(s)
+            got = pipe.buffers(s, B, N)["scores"]
+            assert np.array_equal(got.view(np.uint32), want[which[s]].view(np.uint32)), i
+        b = (i * 5 + i // 7) % n_batches                   # no fixed slot <-> batch pairing
+        v = pipe.buffers(s, B, N)
+        v["guess_idx"][:] = batches[b][0]; v["guess_len"][:] = batches[b][1]
+        v["answer_slot"][:] = batches[b][2]; v["exact"][:] = batches[b][3]
+        v["scores"][:] = -1.0
+        pipe.submit(s, 0.01)
+        which[s] = b
+    for s in range(depth):
+        pipe.wait(s)
+        assert np.array_equal(pipe.buffers(s, B, N)["scores"].view(np.uint32), want[which[s]].view(np.uint32))
     pipe.close()
 
 
