@@ -2,12 +2,13 @@
 //
 // A pipe is a ring of `depth` slots.  Each slot owns a page-locked host block that the caller
 // fills in place (no staging copy), a device block of the same layout, a stream and an event.
-// cm_pipe_submit() enqueues ONE scoring kernel on the slot's stream for batches of ordinary size:
-// the kernel reads the batch from the page-locked block across PCIe and writes the scores back
-// into it, so there is no copy to schedule and the slots' kernels overlap on the GPU (the reads
-// of batch i+1 arrive while batch i is gathering).  Large batches go through the copy engine
-// instead (H2D of the inputs before the kernel, D2H of the scores after it): see the thresholds
-// below.  Either way the host fills batch i+2 meanwhile.
+// cm_pipe_submit() takes one of two routes on the slot's stream:
+//   in place     one scoring kernel that reads the batch from the page-locked block across PCIe
+//                and writes the scores back into it; the slots' kernels overlap on the GPU (the
+//                reads of batch i+1 arrive while batch i is gathering)
+//   copy engine  H2D copy of the inputs, kernel, D2H copy of the scores
+// chosen by batch size and, for mid-size batches, by timing both (see the constants below).
+// Either way the host fills batch i+2 meanwhile.
 //
 // This is the device-side half of the request micro-batcher that north_star places in
 // src/server.py (cassmantle_b200/server.py drives it); the reference has no counterpart.

@@ -130,10 +130,12 @@ int cm_score_batch_host(cm_engine *e,
  * No reference counterpart: the reference scores one request at a time inside its event
  * loop (src/backend.py:312-317).  This is the device half of the request micro-batcher that
  * north_star adds to src/server.py.  A pipe is a ring of `depth` slots; each slot owns a
- * page-locked host block that the caller fills IN PLACE.  Up to 8192 guesses (and 640 KiB of
- * packed inputs) a step is ONE kernel that reads the block and writes the scores into it
- * across PCIe; larger batches are moved by the copy engine (H2D, kernel, D2H on the slot's
- * stream).  The slot's contents must not be touched between submit and wait.
+ * page-locked host block that the caller fills IN PLACE.  A step is either ONE kernel that
+ * reads the block and writes the scores into it across PCIe (always for inputs up to 64 KiB),
+ * or H2D copy, kernel, D2H copy on the slot's stream (always above 8192 guesses or 640 KiB);
+ * in between the pipe times both routes as it runs and keeps the faster one (environment
+ * CM_PIPE_ROUTE=inplace|copy pins it).  Results do not depend on the route.  The slot's
+ * contents must not be touched between submit and wait.
  *
  *   cm_pipe_buffers(p, s, B, N, &idx, &len, &slot, &exact, &scores, &centi)   fill these
  *   cm_pipe_submit(p, s, min_score, want_centi)                                asynchronous
