@@ -36,9 +36,10 @@ for k, r in enumerate(rows[2:]):
         if w in col:
             print(f"{w:72s} {r[col[w]]:>16s} {units[col[w]]}")
     try:
-        rd = float(r[col["dram__bytes_read.sum"]]); wr = float(r[col["dram__bytes_write.sum"]])
-        u = units[col["dram__bytes_read.sum"]]
-        print(f"{'traffic = dram read + write':72s} {rd + wr:16.3f} {u}")
+        scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        rd = float(r[col["dram__bytes_read.sum"]]) * scale[units[col["dram__bytes_read.sum"]]]
+        wr = float(r[col["dram__bytes_write.sum"]]) * scale[units[col["dram__bytes_write.sum"]]]
+        print(f"{'traffic = dram read + write':72s} {(rd + wr) / 1e6:16.3f} Mbyte")
     except Exception:
         pass
 src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
