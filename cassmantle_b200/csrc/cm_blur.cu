@@ -25,6 +25,7 @@
 
 #include <cmath>
 #include <cstring>
+#include <algorithm>
 #include <new>
 #include <vector>
 
@@ -40,6 +41,8 @@ struct cm_blur {
     uint8_t *h_pin = nullptr;         // pinned staging for results
     void *d_params = nullptr;         // BoxParams[max_batch]
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;   // results of chunk i travel while chunk i+1 is blurred
+    cudaEvent_t blurred[2] = {nullptr, nullptr};
     std::mutex mu;
 };
 
@@ -168,13 +171,13 @@ cm_boxblur_kernel(const uint8_t *__restrict__ src, size_t src_req_stride, uint8_
 
 template <int C>
 int launch_pass(cm_blur *b, const uint8_t *src, size_t src_req_stride, uint8_t *dst, size_t dst_req_stride,
-                int n_lines, int n, size_t line_stride, size_t pix_stride, int batch) {
+                int n_lines, int n, size_t line_stride, size_t pix_stride, int batch, const void *params) {
     const size_t smem = (size_t)C * (n + 1) * sizeof(uint32_t) + (size_t)n * C;
     // per device and cheap: set it on every launch rather than cache a process-wide flag
     if (smem > 48 * 1024)
         CM_CUDA(cudaFuncSetAttribute(cm_boxblur_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cm_boxblur_kernel<C><<<dim3((unsigned)n_lines, (unsigned)batch), 256, smem, b->stream>>>(
-        src, src_req_stride, dst, dst_req_stride, n, line_stride, pix_stride, (const BoxParams *)b->d_params);
+        src, src_req_stride, dst, dst_req_stride, n, line_stride, pix_stride, (const BoxParams *)params);
     cm::count_launch();
     CM_CUDA(cudaGetLastError());
     return CM_OK;
@@ -217,21 +220,24 @@ int launch_transpose(cm_blur *b, const uint8_t *src, uint8_t *dst, int h, int w,
     return CM_OK;
 }
 
+// Sessions [first, first + batch): three passes along x, transpose, three along x, transpose back.
+// The result is in d_b.
 template <int C>
-int blur_batch(cm_blur *b, int batch, uint8_t **result) {
+int blur_batch(cm_blur *b, int first, int batch) {
     const size_t img = (size_t)b->h * b->w * C;
     const size_t row = (size_t)b->w * C, col = (size_t)b->h * C;
+    uint8_t *a = b->d_a + (size_t)first * img, *o = b->d_b + (size_t)first * img;
+    const void *pr = static_cast<const BoxParams *>(b->d_params) + first;
     // along x: lines are rows
-    if (int rc = launch_pass<C>(b, b->d_src, 0, b->d_a, img, b->h, b->w, row, C, batch)) return rc;
-    if (int rc = launch_pass<C>(b, b->d_a, img, b->d_b, img, b->h, b->w, row, C, batch)) return rc;
-    if (int rc = launch_pass<C>(b, b->d_b, img, b->d_a, img, b->h, b->w, row, C, batch)) return rc;
+    if (int rc = launch_pass<C>(b, b->d_src, 0, a, img, b->h, b->w, row, C, batch, pr)) return rc;
+    if (int rc = launch_pass<C>(b, a, img, o, img, b->h, b->w, row, C, batch, pr)) return rc;
+    if (int rc = launch_pass<C>(b, o, img, a, img, b->h, b->w, row, C, batch, pr)) return rc;
     // along y: transpose, blur the (now contiguous) columns, transpose back -- as Pillow does
-    if (int rc = launch_transpose<C>(b, b->d_a, b->d_b, b->h, b->w, img, batch)) return rc;
-    if (int rc = launch_pass<C>(b, b->d_b, img, b->d_a, img, b->w, b->h, col, C, batch)) return rc;
-    if (int rc = launch_pass<C>(b, b->d_a, img, b->d_b, img, b->w, b->h, col, C, batch)) return rc;
-    if (int rc = launch_pass<C>(b, b->d_b, img, b->d_a, img, b->w, b->h, col, C, batch)) return rc;
-    if (int rc = launch_transpose<C>(b, b->d_a, b->d_b, b->w, b->h, img, batch)) return rc;
-    *result = b->d_b;
+    if (int rc = launch_transpose<C>(b, a, o, b->h, b->w, img, batch)) return rc;
+    if (int rc = launch_pass<C>(b, o, img, a, img, b->w, b->h, col, C, batch, pr)) return rc;
+    if (int rc = launch_pass<C>(b, a, img, o, img, b->w, b->h, col, C, batch, pr)) return rc;
+    if (int rc = launch_pass<C>(b, o, img, a, img, b->w, b->h, col, C, batch, pr)) return rc;
+    if (int rc = launch_transpose<C>(b, a, o, b->w, b->h, img, batch)) return rc;
     return CM_OK;
 }
 
@@ -244,6 +250,9 @@ int cm_blur_destroy(cm_blur *b) {
     {
         cm::DeviceGuard guard(b->device);
         if (b->stream) { cudaStreamSynchronize(b->stream); cudaStreamDestroy(b->stream); }
+        if (b->copy_stream) { cudaStreamSynchronize(b->copy_stream); cudaStreamDestroy(b->copy_stream); }
+        for (cudaEvent_t ev : b->blurred)
+            if (ev) cudaEventDestroy(ev);
         if (b->d_src) cudaFree(b->d_src);
         if (b->d_a) cudaFree(b->d_a);
         if (b->d_b) cudaFree(b->d_b);
@@ -276,6 +285,9 @@ int cm_blur_create(cm_blur **out, int device, int max_height, int max_width, int
     if (err == cudaSuccess) err = cudaMalloc(&b->d_params, sizeof(BoxParams) * max_batch);
     if (err == cudaSuccess) err = cudaHostAlloc(&b->h_pin, img * max_batch, cudaHostAllocDefault);
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking);
+    if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&b->copy_stream, cudaStreamNonBlocking);
+    for (cudaEvent_t &ev : b->blurred)
+        if (err == cudaSuccess) err = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
     if (err != cudaSuccess) {
         cudaGetLastError();
         const int code = fail(CM_ERR_NOMEM, "blur buffers (%zu bytes x %d) failed: %s", img, 2 * max_batch + 1,
@@ -300,11 +312,8 @@ int cm_blur_set_image(cm_blur *b, const uint8_t *pixels, int height, int width) 
     return CM_OK;
 }
 
-int cm_blur_batch_host(cm_blur *b, const float *radii, int n, uint8_t *out) {
-    if (b == nullptr) return fail(CM_ERR_INVALID, "blur is NULL");
-    if (n < 0 || n > b->max_batch) return fail(CM_ERR_INVALID, "n %d outside [0, %d]", n, b->max_batch);
-    if (n == 0) return CM_OK;
-    if (radii == nullptr || out == nullptr) return fail(CM_ERR_INVALID, "radii or out is NULL");
+// Blurs into the device ping-pong buffers and brings the n images back into b->h_pin (b->mu held).
+static int blur_batch_to_pinned(cm_blur *b, const float *radii, int n, size_t *bytes_out) {
     if (b->h == 0) return fail(CM_ERR_STATE, "cm_blur_set_image has not been called");
     std::vector<BoxParams> params((size_t)n);
     for (int i = 0; i < n; ++i) {
@@ -312,21 +321,55 @@ int cm_blur_batch_host(cm_blur *b, const float *radii, int n, uint8_t *out) {
             return fail(CM_ERR_INVALID, "radius %g of request %d outside [0, 4096]", (double)radii[i], i);
         params[(size_t)i] = box_params(radii[i]);
     }
-    std::lock_guard<std::mutex> lock(b->mu);
     cm::DeviceGuard guard(b->device);
     CM_CUDA(cudaMemcpyAsync(b->d_params, params.data(), sizeof(BoxParams) * n, cudaMemcpyHostToDevice, b->stream));
-    uint8_t *result = nullptr;
-    int rc;
-    switch (b->channels) {
-        case 1: rc = blur_batch<1>(b, n, &result); break;
-        case 3: rc = blur_batch<3>(b, n, &result); break;
-        default: rc = blur_batch<4>(b, n, &result); break;
+    // In chunks of about 16 MB of pixels: while one chunk is being blurred the previous one is
+    // already on its way to the host (1024x1024 RGB: the copy is the longer of the two).
+    const size_t img = (size_t)b->h * b->w * b->channels;
+    const int chunk = (int)std::max<size_t>(1, std::min<size_t>((size_t)n, ((size_t)16 << 20) / img));
+    int k = 0;
+    for (int first = 0; first < n; first += chunk, ++k) {
+        const int count = std::min(chunk, n - first);
+        int rc;
+        switch (b->channels) {
+            case 1: rc = blur_batch<1>(b, first, count); break;
+            case 3: rc = blur_batch<3>(b, first, count); break;
+            default: rc = blur_batch<4>(b, first, count); break;
+        }
+        if (rc != CM_OK) return rc;
+        CM_CUDA(cudaEventRecord(b->blurred[k & 1], b->stream));
+        CM_CUDA(cudaStreamWaitEvent(b->copy_stream, b->blurred[k & 1], 0));
+        CM_CUDA(cudaMemcpyAsync(b->h_pin + (size_t)first * img, b->d_b + (size_t)first * img, (size_t)count * img,
+                                cudaMemcpyDeviceToHost, b->copy_stream));
     }
-    if (rc != CM_OK) return rc;
-    const size_t bytes = (size_t)b->h * b->w * b->channels * n;
-    CM_CUDA(cudaMemcpyAsync(b->h_pin, result, bytes, cudaMemcpyDeviceToHost, b->stream));
+    CM_CUDA(cudaStreamSynchronize(b->copy_stream));
     CM_CUDA(cudaStreamSynchronize(b->stream));
+    const size_t bytes = img * n;
+    *bytes_out = bytes;
+    return CM_OK;
+}
+
+int cm_blur_batch_host(cm_blur *b, const float *radii, int n, uint8_t *out) {
+    if (b == nullptr) return fail(CM_ERR_INVALID, "blur is NULL");
+    if (n < 0 || n > b->max_batch) return fail(CM_ERR_INVALID, "n %d outside [0, %d]", n, b->max_batch);
+    if (n == 0) return CM_OK;
+    if (radii == nullptr || out == nullptr) return fail(CM_ERR_INVALID, "radii or out is NULL");
+    std::lock_guard<std::mutex> lock(b->mu);
+    size_t bytes = 0;
+    if (int rc = blur_batch_to_pinned(b, radii, n, &bytes)) return rc;
     memcpy(out, b->h_pin, bytes);
+    return CM_OK;
+}
+
+int cm_blur_batch_pinned(cm_blur *b, const float *radii, int n, const uint8_t **out) {
+    if (b == nullptr) return fail(CM_ERR_INVALID, "blur is NULL");
+    if (n < 1 || n > b->max_batch) return fail(CM_ERR_INVALID, "n %d outside [1, %d]", n, b->max_batch);
+    if (radii == nullptr || out == nullptr) return fail(CM_ERR_INVALID, "radii or out is NULL");
+    *out = nullptr;
+    std::lock_guard<std::mutex> lock(b->mu);
+    size_t bytes = 0;
+    if (int rc = blur_batch_to_pinned(b, radii, n, &bytes)) return rc;
+    *out = b->h_pin;
     return CM_OK;
 }
 

@@ -210,6 +210,10 @@ int cm_blur_create(cm_blur **out, int device, int max_height, int max_width, int
 int cm_blur_destroy(cm_blur *b);
 int cm_blur_set_image(cm_blur *b, const uint8_t *pixels, int height, int width);
 int cm_blur_batch_host(cm_blur *b, const float *radii, int n, uint8_t *out);
+/* The same, without the last host copy: *out points at the n images in the blur's own
+ * page-locked result block, valid until the next call on `b` (a consumer that encodes or sends
+ * the pixels right away -- src/server.py:131-133 saves them as JPEG -- needs no more).      */
+int cm_blur_batch_pinned(cm_blur *b, const float *radii, int n, const uint8_t **out);
 
 /* ---- several GPUs: score all-gather over NVLink peer memory ---------------------------- *
  * No reference counterpart (the reference has no collective).  SURVEY.md §8e: one process

@@ -19,6 +19,11 @@ def test_golden_outputs_of_real_pillow():
     blur.set_image(g["image"])
     got = blur.blur_radii(g["radii"])
     assert np.array_equal(got, g["outputs"])
+    view = blur.blur_radii(g["radii"], copy=False)               # cm_blur_batch_pinned: no host copy
+    assert not view.flags.writeable and np.array_equal(view, g["outputs"])
+    first = view[:3].copy()
+    again = blur.blur_radii(g["radii"][:3], copy=False)          # the block is reused by the next call
+    assert np.array_equal(again, first)
     blur.close()
 
 
@@ -52,6 +57,7 @@ def test_mask_image_reference_signature_and_full_size():
     blur.set_image(pil)
     scores = [0.01, 0.4567891, 0.7071068, 0.99999994, 1.0, 0.1, 0.25, 0.9]
     got = blur.mask_images(scores)
+    assert np.array_equal(blur.mask_images(scores, copy=False), got)
     for s, x in zip(scores, got):
         want = np.asarray(pil.filter(ImageFilter.GaussianBlur(blur.score_to_blur(s))))     # src/backend.py:322-324
         assert np.array_equal(x, want), s
