@@ -660,14 +660,23 @@ def run_own(args) -> None:
 
         async def rounds():
             mb = MicroBatcher(be, max_batch=512, max_delay_s=0.0005)
-            ts2 = [await one_round(mb) for _ in range(30)]
+            ts2 = [await one_round(mb) for _ in range(60)]
             mb.close()
             return ts2, mb.batches
 
+        # A 3M-word vocabulary is 6M long-lived Python objects: a full collection walks all of them
+        # in the middle of some request (tens of ms).  gc.freeze() after start-up takes them out of
+        # the collector's sight, as INTEGRATION.md section 7 tells a server to do.
+        import gc
+        gc.collect()
+        gc.freeze()
         ts2, n_batches = asyncio.run(rounds())
+        gc.unfreeze()
         ts2 = np.sort(np.asarray(ts2[5:])) * 1e3
-        py_lat = {"workload": "256 concurrent compute_scores requests x 2 words (strings), MicroBatcher + Backend",
-                  "p50_ms": float(ts2[len(ts2) // 2]), "p99_ms": float(ts2[-1]), "device_batches_per_round": n_batches / 30}
+        py_lat = {"workload": "256 concurrent compute_scores requests x 2 words (strings), MicroBatcher + Backend, "
+                              "gc.freeze() after the vocabulary is built",
+                  "p50_ms": float(ts2[len(ts2) // 2]), "p99_ms": float(ts2[int(len(ts2) * 0.99)]),
+                  "max_ms": float(ts2[-1]), "rounds": int(len(ts2)), "device_batches_per_round": n_batches / 60}
         eng.set_answers(ans)
         eng.synchronize()
 
