@@ -99,6 +99,7 @@ def test_golden_synth_cases(small_engine, golden):
     (1, 1, False), (7, 1, False), (64, 1, False), (512, 8, False), (513, 8, True),
     (4096, 1, False), (4096, 16, False), (1000, 16, True), (300, 33, True), (129, 64, True),
     (50, 100, True), (4096, 16, True), (2500, 40, True),     # >= 32768 rows: the 16-lane paired kernel
+    (3, 4096, True), (9, 4096, False),                       # CM_MAX_SEQ word slots per guess
 ])
 def test_batch_matches_oracle(small_engine, small_table, B, N, ragged):
     idx, ln, ans, slot, ex = synth.make_guess_batch(B, N, 50_000, n_answers=3, seed=B * 131 + N,
