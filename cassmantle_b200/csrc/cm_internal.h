@@ -60,6 +60,7 @@ bool is_pinned_host(const void *p);
 int check_engine(const cm_engine *e);
 
 void similar_state_free(cm_engine *e);     // cm_similar.cu
+int ensure_stage(cm_engine *e, size_t bytes);   // e->h_stage holds at least `bytes` (call with e->mu held)
 void similar_invalidate(cm_engine *e);     // the table changed: cached row norms are stale
 
 // Validates the arguments and enqueues the scoring kernel; pointers may be device memory or

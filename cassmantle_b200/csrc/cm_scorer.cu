@@ -783,7 +783,7 @@ static void parallel_memcpy(unsigned char *dst, const unsigned char *src, size_t
 }
 
 // Pinned staging block of the host entry point (only used when the caller's memory is pageable).
-static int ensure_stage(cm_engine *e, size_t bytes) {
+int ensure_stage(cm_engine *e, size_t bytes) {
     if (bytes <= e->stage_bytes) return CM_OK;
     size_t want = e->stage_bytes ? e->stage_bytes : (size_t)1 << 20;
     while (want < bytes) want *= 2;

@@ -194,6 +194,17 @@ int cm_score_words_host(cm_engine *e, cm_vocab *v,
  * norms (gensim's fill_norms).  NaN cosines rank last.                                       */
 int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_out, float *sims_out, int *n_out);
 
+/* ---- mask selection, numeric half ------------------------------------- *
+ * semantic_distance(word, word_list, model), src/utils.py:73-79, for every word of word_list
+ * at once (select_descriptive_words calls it in a loop, src/utils.py:91):
+ *   out[i] = || table[rows[i]] - mean_j table[rows[j]] ||_2   j < n_mean with rows[j] >= 0,
+ *   out[i] = 0 where rows[i] < 0 (`word in model` is false),           for all i < n.
+ * word_list is rows[0 .. n_mean); n_mean == n scores the list against itself, as the reference
+ * does; rows beyond n_mean are extra words measured against the same mean.
+ * numpy's operation order: fp32 running sum in list order, / count, fp32 difference,
+ * sqrt(dot).  Host pointers, blocking; n <= CM_MAX_SEQ.  Once per round in the reference.     */
+int cm_semantic_distances(cm_engine *e, const int32_t *rows, int n, int n_mean, float *out);
+
 /* ---- per-session image blur ---------------------------------------- *
  * Backend.mask_image, src/backend.py:322-324: image.filter(ImageFilter.GaussianBlur(blur))
  * with blur = score_to_blur(score) (src/backend.py:319-320), run per request by
