@@ -28,7 +28,10 @@ for ``KeyedVectors.similarity`` / ``matutils.unitvec``:
 scipy is installed here, so ``unitvec`` below calls the very same BLAS entry
 points gensim binds.  The outputs are pinned only by the known-answer cases in
 ``tests/golden/scorer_kat.json`` (authored in this repo from the semantics
-above; generator: ``tests/golden/make_golden.py``).
+above; generator: ``tests/golden/make_golden.py``).  What IS checked against the reference's
+own code, live, is part (a): ``tests/test_reference_backend.py`` imports ``src/backend.py``
+unmodified and runs its ``compute_score`` / ``compute_scores`` with ``OracleWordVectors`` as
+``self.wv``; only the arithmetic inside gensim stays a restatement.
 
 Extension (labelled, SURVEY.md §0 Track A): a guess of N > 1 words is mean-pooled
 exactly like gensim's classic ``n_similarity`` -- ``array(rows).mean(axis=0)`` ->
