@@ -718,8 +718,10 @@ def run_own(args) -> None:
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of cm_score_kernel at 4096x16 from the
-# committed `ncu --set full` capture (profiles/).
-TRAFFIC_BYTES_PER_LAUNCH = 81_622_272   # profiles/r1_v4_4096x16.summary.txt (79.76 MB read + 1.86 MB written)
+# committed `ncu --set full` capture of the kernel timed above (row loads carry the .L2::64B hint):
+# profiles/r1_v5_4096x16.summary.txt, 75,981,568 B read + 2,135,552 B written.  Algorithmic bytes
+# are 78,938,112: a few rows repeat within a batch and come from L2.  (r1_v4, before the hint: 81,622,272.)
+TRAFFIC_BYTES_PER_LAUNCH = 78_117_120
 
 
 def main() -> None:

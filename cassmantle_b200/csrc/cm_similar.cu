@@ -54,7 +54,7 @@ cm_row_norm_kernel(const float *__restrict__ table, int64_t n_rows, int dim4, fl
     for (int64_t r = warp; r < n_rows; r += n_warps) {
         float s = 0.f;
         for (int j = lane; j < dim4; j += 32) {
-            const float4 v = cm::ld_stream_f4(t4 + r * dim4 + j);
+            const float4 v = cm::ld_stream_seq_f4(t4 + r * dim4 + j);
             s = fmaf(v.x, v.x, s); s = fmaf(v.y, v.y, s); s = fmaf(v.z, v.z, s); s = fmaf(v.w, v.w, s);
         }
         s = cm::warp_sum(s);
@@ -145,7 +145,7 @@ cm_scan_kernel(const float *__restrict__ table, int64_t n_rows, int dim4, const 
             for (int v = 0; v < VPL; ++v) {
                 const int j = lane + 32 * v;
                 if (r < n_rows && j < dim4) {
-                    const float4 x = cm::ld_stream_f4(t4 + r * dim4 + j);
+                    const float4 x = cm::ld_stream_seq_f4(t4 + r * dim4 + j);
                     s = fmaf(x.x, q[v].x, s); s = fmaf(x.y, q[v].y, s);
                     s = fmaf(x.z, q[v].z, s); s = fmaf(x.w, q[v].w, s);
                 }
