@@ -22,6 +22,7 @@
 #include <vector>
 
 #include "cm_internal.h"
+#include "cm_route_tuner.h"
 
 struct cm_pipe_slot {
     unsigned char *h = nullptr;     // pinned: [idx | len | slot | exact | scores | centi]
@@ -40,14 +41,7 @@ struct cm_pipe {
     std::vector<cm_pipe_slot> slots;
     size_t direct_in_max = 0;       // inputs up to this many bytes are read in place by the kernel
     int direct_out_max = 0;         // up to this many guesses the kernel writes scores in place
-    // Mid-size batches (kSmallIn < inputs <= direct_in_max): which route is faster depends on how
-    // busy the PCIe path is, so the pipe times both and keeps the better one (see pick_route).
-    enum Route { kAuto, kInPlace, kCopy } route = kAuto;
-    enum Phase { kWarm, kTryInPlace, kTryCopy, kHold } phase = kWarm;
-    int phase_submits = 0;
-    bool best_in_place = true;
-    std::chrono::steady_clock::time_point window_start;
-    double window_s[2] = {0.0, 0.0};          // [in place, copy engine] seconds per timed window
+    cm::RouteTuner tuner;           // mid-size batches (kSmallIn < inputs <= direct_in_max): cm_route_tuner.h
 };
 
 namespace {
@@ -73,43 +67,10 @@ constexpr size_t kDirectOutMax = 8192;        // guesses; also caps the direct-i
 
 // Up to this many input bytes a step is bound by launch/enqueue cost, not by PCIe: always in place.
 constexpr size_t kSmallIn = 64u << 10;
-// Route tuning for mid-size batches: skip the start-up, then time kWindow submits on each route
-// (after kSettle submits, so that batches submitted on the other route have drained), keep the
-// winner for kHold submits, and try again.  The copy engine has to win by 3 % to be chosen: when
-// the producer is the bottleneck both windows measure the producer, and in place costs the host
-// one call per step instead of three.
-constexpr int kWarmSubmits = 64, kSettle = 32, kWindow = 256, kHold = 16384;
-
 // true: this mid-size batch goes in place; false: through the copy engine
 bool pick_route(cm_pipe *p) {
-    if (p->route != cm_pipe::kAuto) return p->route == cm_pipe::kInPlace;
-    const int n = ++p->phase_submits;
-    switch (p->phase) {
-        case cm_pipe::kWarm:
-            if (n >= kWarmSubmits) { p->phase = cm_pipe::kTryInPlace; p->phase_submits = 0; }
-            return true;
-        case cm_pipe::kTryInPlace:
-        case cm_pipe::kTryCopy: {
-            const bool in_place = p->phase == cm_pipe::kTryInPlace;
-            if (n == kSettle) p->window_start = std::chrono::steady_clock::now();
-            if (n == kSettle + kWindow) {
-                p->window_s[in_place ? 0 : 1] =
-                    std::chrono::duration<double>(std::chrono::steady_clock::now() - p->window_start).count();
-                p->phase_submits = 0;
-                if (in_place) {
-                    p->phase = cm_pipe::kTryCopy;
-                } else {
-                    p->best_in_place = !(p->window_s[1] < 0.97 * p->window_s[0]);
-                    p->phase = cm_pipe::kHold;
-                }
-            }
-            return in_place;
-        }
-        case cm_pipe::kHold:
-            if (n >= kHold) { p->phase = cm_pipe::kTryInPlace; p->phase_submits = 0; }
-            return p->best_in_place;
-    }
-    return true;
+    const double now = std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+    return p->tuner.next(now);
 }
 
 size_t env_size(const char *name, size_t fallback) {
@@ -163,8 +124,8 @@ int cm_pipe_create(cm_pipe **out, cm_engine *e, int depth, int max_guesses, int 
     p->direct_in_max = env_size("CM_PIPE_DIRECT_IN_MAX", kDirectInMax);
     p->direct_out_max = (int)env_size("CM_PIPE_DIRECT_OUT_MAX", kDirectOutMax);
     if (const char *r = getenv("CM_PIPE_ROUTE")) {          // "inplace" | "copy" pin the mid-size route
-        if (strcmp(r, "inplace") == 0) p->route = cm_pipe::kInPlace;
-        else if (strcmp(r, "copy") == 0) p->route = cm_pipe::kCopy;
+        if (strcmp(r, "inplace") == 0) p->tuner.pin(cm::RouteTuner::kInPlace);
+        else if (strcmp(r, "copy") == 0) p->tuner.pin(cm::RouteTuner::kCopy);
     }
     cm::DeviceGuard guard(e->device);
     for (auto &s : p->slots) {
