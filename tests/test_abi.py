@@ -54,3 +54,27 @@ def test_no_cpu_fallback_without_gpu(lib):
     from cassmantle_b200.engine import ScoringEngine
     with pytest.raises(_lib.CassMantleError):
         ScoringEngine(100, 300)
+
+
+def test_product_package_never_touches_the_oracle():
+    """oracle/ is test infrastructure: nothing under cassmantle_b200/ may import, load or run it,
+    and there is no CPU fallback behind the CUDA extension."""
+    import ast
+    import glob
+    import os
+    pkg = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "cassmantle_b200")
+    files = glob.glob(os.path.join(pkg, "**", "*.py"), recursive=True)
+    assert len(files) >= 8
+    for path in files:
+        src = open(path).read()
+        for node in ast.walk(ast.parse(src)):
+            names = []
+            if isinstance(node, ast.Import):
+                names = [a.name for a in node.names]
+            elif isinstance(node, ast.ImportFrom):
+                names = [node.module or ""]
+            assert not any(n == "oracle" or n.startswith("oracle.") for n in names), path
+        assert "liboracle" not in src and "oracle/" not in src.replace("oracle/ is", ""), path
+    for path in glob.glob(os.path.join(pkg, "csrc", "*")):
+        text = open(path, errors="ignore").read()
+        assert "oracle/" not in text and "liboracle" not in text and "dlopen" not in text, path
