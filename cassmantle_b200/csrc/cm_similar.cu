@@ -168,6 +168,75 @@ cm_scan_kernel(const float *__restrict__ table, int64_t n_rows, int dim4, const 
     if (sh_hist8[threadIdx.x]) atomicAdd(&ps->hist8[threadIdx.x], sh_hist8[threadIdx.x]);
 }
 
+// The scan laid out like the scoring kernel's gather (rows of 65..80 float4, i.e. 300-d): 16 lanes
+// x 5 vectors per row, two rows per load instruction, one half-warp walks 16 consecutive rows
+// keeping one partial dot product per row, and a 15-shuffle transpose-reduce at the end leaves
+// row r0 + sub's distance in lane sub.  Many short CTAs (128 rows each, 7 per SM) instead of a
+// persistent grid.  Each row is staged in an explicit register buffer: written with the load
+// inside the FMA loop, ptxas leaves every load alone between its four FFMAs (one load in flight
+// per lane, 948 us per query); staged, it keeps about 13 loads in flight per lane.
+template <int VPL>
+__global__ void __launch_bounds__(128, 7)
+cm_scan16_kernel(const float *__restrict__ table, int64_t n_rows, int dim4, const float *__restrict__ mean,
+                 const float *__restrict__ norms, float *__restrict__ dists, PickState *__restrict__ ps) {
+    constexpr int LPG = 16, ROWS = 16;
+    __shared__ unsigned sh_hist8[256];
+    sh_hist8[threadIdx.x] = 0;
+    sh_hist8[threadIdx.x + 128] = 0;
+    __syncthreads();
+    cm::pdl_launch_dependents();
+    cm::pdl_wait();                                     // the query kernel wrote `mean`
+    const int lane = threadIdx.x & 31;
+    const int sub = lane & (LPG - 1);
+    const int64_t half = (int64_t)blockIdx.x * (128 / LPG) + (threadIdx.x / LPG);
+    const int64_t r0 = half * ROWS;
+    const float4 *t4 = reinterpret_cast<const float4 *>(table);
+    if (r0 - (int64_t)(lane / LPG) * ROWS < n_rows) {   // warp-uniform: the warp's first half-warp has rows
+        float4 q[VPL];
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+            const int j = sub + LPG * v;
+            q[v] = j < dim4 ? reinterpret_cast<const float4 *>(mean)[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        const int64_t my_row = r0 + sub;
+        const float nrm = my_row < n_rows ? norms[my_row] : 1.f;
+        float p[ROWS];
+#pragma unroll
+        for (int k = 0; k < ROWS; ++k) {
+            const int64_t r = r0 + k;
+            float4 buf[VPL];                            // the whole row is requested before any of it is used
+#pragma unroll
+            for (int v = 0; v < VPL; ++v) {
+                const int j = sub + LPG * v;
+                buf[v] = (r < n_rows && j < dim4) ? cm::ld_stream_seq_f4(t4 + r * dim4 + j)
+                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            float s = 0.f;
+#pragma unroll
+            for (int v = 0; v < VPL; ++v) {
+                s = fmaf(buf[v].x, q[v].x, s); s = fmaf(buf[v].y, q[v].y, s);
+                s = fmaf(buf[v].z, q[v].z, s); s = fmaf(buf[v].w, q[v].w, s);
+            }
+            p[k] = s;
+        }
+        // transpose-reduce: after the stage with offset o a lane keeps the rows whose bit o matches its own
+#pragma unroll
+        for (int o = ROWS / 2; o > 0; o >>= 1) {
+            const bool upper = (sub & o) != 0;
+#pragma unroll
+            for (int j = 0; j < o; ++j) {
+                const float send = upper ? p[j] : p[j + o];
+                const float keep = upper ? p[j + o] : p[j];
+                p[j] = keep + __shfl_xor_sync(cm::kFullMask, send, o);
+            }
+        }
+        if (my_row < n_rows) emit_dist(my_row, p[0], nrm, dists, ps->hist16, sh_hist8);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 256; i += 128)
+        if (sh_hist8[i]) atomicAdd(&ps->hist8[i], sh_hist8[i]);
+}
+
 // Which of 256 bins, scanned from bin 255 downwards, holds the k-th entry; *above = entries in
 // the bins before it.  Called by one full warp; every lane returns the same answer.
 __device__ int find_bin_from_top(const unsigned *h, unsigned k, unsigned *above) {
@@ -497,6 +566,13 @@ extern "C" int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_o
         return (unsigned)(c < 0 ? 0 : (c > kBucketCap ? kBucketCap : c));
     }();
     const float *table = e->d_table, *mean = s->d_mean, *norms = s->d_norms;
+    // CM_SCAN16=1 selects the experimental 16-lane scan for 300-d tables (see cm_scan16_kernel)
+    static const bool scan16 = [] { const char *v = getenv("CM_SCAN16"); return v != nullptr && *v == '1'; }();
+    if (scan16 && dim4 > 64 && dim4 <= 80) {
+        cfg.blockDim = dim3(128);
+        cfg.gridDim = dim3((unsigned)((e->n_rows + 127) / 128));
+        cudaLaunchKernelEx(&cfg, cm_scan16_kernel<5>, table, e->n_rows, dim4, mean, norms, s->d_dists, s->d_pick);
+    } else {
     cfg.blockDim = dim3(256);
 #define CM_CASE(V, MB)                                                                             \
     case V:                                                                                        \
@@ -511,6 +587,7 @@ extern "C" int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_o
             break;
     }
 #undef CM_CASE
+    }
     cm::count_launch();
     cfg.gridDim = dim3(148 * 4);
     cfg.blockDim = dim3(256);
