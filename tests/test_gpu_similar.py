@@ -139,3 +139,46 @@ def test_most_similar_other_dimensions(dim):
         for q, k in ((0, 5), (3000, 100)):
             rows, sims = eng.most_similar(q, k)
             _check(rows, sims, O.most_similar_dists(vec, q), k, q)
+
+
+def _similar_child(env_extra, n_rows, queries):
+    """most_similar in a child process (the scan variant is read once per process)."""
+    import os, subprocess, sys, textwrap
+    code = textwrap.dedent(f"""
+        import numpy as np
+        from cassmantle_b200.engine import ScoringEngine
+        with ScoringEngine.synthetic({n_rows}, 300, seed=3) as eng:
+            for q, k in {queries!r}:
+                r, s = eng.most_similar(q, k)
+                print(q, k, " ".join(map(str, r.tolist())), " ".join(v.hex() for v in s.astype(np.float64)))
+    """)
+    env = dict(os.environ)
+    env.pop("CM_SCAN16", None)
+    env.update(env_extra)
+    return subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, check=True,
+                          cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__)))).stdout.splitlines()
+
+
+def _compare_scans(n_rows, queries):
+    a = _similar_child({}, n_rows, queries)
+    b = _similar_child({"CM_SCAN16": "1"}, n_rows, queries)
+    assert len(a) == len(b) == len(queries)
+    for la, lb in zip(a, b):
+        fa, fb = la.split(" "), lb.split(" ")
+        k = int(fa[1])
+        assert fa[:2] == fb[:2]
+        rows_a, rows_b = fa[2:2 + k], fb[2:2 + k]
+        sims_a = np.array([float.fromhex(x) for x in fa[2 + k:]])
+        sims_b = np.array([float.fromhex(x) for x in fb[2 + k:]])
+        assert np.abs(sims_a - sims_b).max() <= COS_TOL             # the two scans sum a row in different orders
+        assert fa[0] in rows_a and fa[0] in rows_b                    # the query itself is in both lists
+        assert len(set(rows_a) ^ set(rows_b)) <= 2                   # at most a last-ulp swap at the k-th place
+
+
+def test_opt_in_16_lane_scan_agrees_with_the_default():
+    _compare_scans(50_000, [(5, 1), (77, 51), (4242, 1024)])
+
+
+@pytest.mark.xfail(reason="opt-in kernel (CM_SCAN16=1): its first run at 3,000,000 rows happens here", strict=False)
+def test_opt_in_16_lane_scan_at_full_size():
+    _compare_scans(synth.FULL_ROWS, [(2_718_281, 51), (7, 200)])
