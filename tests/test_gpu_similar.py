@@ -170,9 +170,9 @@ def _compare_scans(n_rows, queries):
         rows_a, rows_b = fa[2:2 + k], fb[2:2 + k]
         sims_a = np.array([float.fromhex(x) for x in fa[2 + k:]])
         sims_b = np.array([float.fromhex(x) for x in fb[2 + k:]])
-        assert np.abs(sims_a - sims_b).max() <= COS_TOL             # the two scans sum a row in different orders
+        assert np.abs(sims_a - sims_b).max() <= 2 * COS_TOL         # each is within COS_TOL of the oracle
         assert fa[0] in rows_a and fa[0] in rows_b                    # the query itself is in both lists
-        assert len(set(rows_a) ^ set(rows_b)) <= 2                   # at most a last-ulp swap at the k-th place
+        assert len(set(rows_a) ^ set(rows_b)) <= 4                   # at most a couple of last-ulp swaps at the k-th place
 
 
 def test_opt_in_16_lane_scan_agrees_with_the_default():
