@@ -317,8 +317,10 @@ static int blur_batch_to_pinned(cm_blur *b, const float *radii, int n, size_t *b
     if (b->h == 0) return fail(CM_ERR_STATE, "cm_blur_set_image has not been called");
     std::vector<BoxParams> params((size_t)n);
     for (int i = 0; i < n; ++i) {
-        if (!(radii[i] >= 0.0f) || radii[i] > 4096.0f)
-            return fail(CM_ERR_INVALID, "radius %g of request %d outside [0, 4096]", (double)radii[i], i);
+        // Pillow squares the radius (_gaussian_blur_radius), so GaussianBlur(-r) == GaussianBlur(r): a
+        // cosine that rounds to 1.0000001 makes score_to_blur slightly negative in the reference too
+        if (!(fabsf(radii[i]) <= 4096.0f))
+            return fail(CM_ERR_INVALID, "radius %g of request %d outside [-4096, 4096]", (double)radii[i], i);
         params[(size_t)i] = box_params(radii[i]);
     }
     cm::DeviceGuard guard(b->device);

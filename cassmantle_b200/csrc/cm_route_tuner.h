@@ -13,6 +13,10 @@
 //   hold      the winner serves kHoldSubmits submits, then the trial is repeated
 // The copy engine has to win by 3 %: when the producer is the bottleneck both windows measure
 // the producer, and in place costs the host one call per step instead of three.
+// The windows are wall time between submits, so they mean "route cost" only while the caller keeps
+// the pipe busy.  A gap of more than kIdleGapS between two submits (two orders of magnitude above
+// a mid-size step) is an idle caller, not a slow route: the current trial window starts again, so
+// bursty or light traffic never completes a trial and stays on the route it had (in place at first).
 #pragma once
 
 namespace cm {
@@ -21,6 +25,7 @@ class RouteTuner {
 public:
     enum Route { kAuto, kInPlace, kCopy };
     static constexpr int kWarmSubmits = 64, kSettle = 32, kWindow = 256, kHoldSubmits = 16384;
+    static constexpr double kIdleGapS = 2e-3;
 
     void pin(Route r) { pinned_ = r; }
     Route pinned() const { return pinned_; }
@@ -29,6 +34,9 @@ public:
     // Returns true when this batch is to go in place, false for the copy engine.
     bool next(double now_s) {
         if (pinned_ != kAuto) return pinned_ == kInPlace;
+        const double gap = now_s - last_s_;
+        last_s_ = now_s;
+        if ((phase_ == kTryInPlace || phase_ == kTryCopy) && count_ > 0 && gap > kIdleGapS) count_ = 0;
         const int n = ++count_;
         switch (phase_) {
             case kWarm:
@@ -67,7 +75,7 @@ private:
     Phase phase_ = kWarm;
     int count_ = 0;
     bool best_in_place_ = true;
-    double window_start_ = 0.0;
+    double window_start_ = 0.0, last_s_ = 0.0;
     double window_s_[2] = {0.0, 0.0};          // [in place, copy engine]
 };
 

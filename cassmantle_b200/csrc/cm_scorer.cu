@@ -336,137 +336,6 @@ cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
 }
 
 // --------------------------------------------------------------------------------------
-// Experimental staging variant (CM_SCORE_VARIANT=40..42): the rows of a guess are fetched by the
-// TMA engine -- cp.async.bulk, one 1200-byte run per row, completion counted on an mbarrier --
-// into a per-warp ring of S shared-memory slots, and reduced from there.  In-flight bytes no
-// longer cost registers (S rows per warp instead of R=2), at the price of a shared-memory round
-// trip.  Same arithmetic and order of additions, hence bit-identical scores.  dim 300 only.
-// Measured (B200, us per launch, overlapped launches) against the register-staged kernel:
-//   4096x16: 12.9 registers | 37.0 (S=4) 29.4 (S=6) 34.7 (S=8);  65536x16: 200 | 348 / 329 / 309.
-// A 1200-byte run is too small a unit for the copy engine (one descriptor-less bulk copy and one
-// mbarrier phase per row), so this stays an experiment; the default path keeps the 16-byte loads.
-// --------------------------------------------------------------------------------------
-template <int S, int THREADS, int MIN_BLOCKS>
-__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
-cm_score_bulk_kernel(const float *__restrict__ table, int64_t n_rows,
-                     const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
-                     int n_guesses, int n_slots,
-                     const float *__restrict__ ans_unit, const int32_t *__restrict__ ans_rows,
-                     int n_answers, const int32_t *__restrict__ answer_slot,
-                     const uint8_t *__restrict__ exact, float min_score,
-                     float *__restrict__ scores, int32_t *__restrict__ centi, uint32_t flags,
-                     int n_ship_ctas, const cm::ShipArgs ship) {
-    constexpr int VPL = 3, DIM4 = 75, ROW_BYTES = 1200, WARPS = THREADS / 32;
-    extern __shared__ __align__(128) unsigned char bulk_smem[];
-    if ((int)blockIdx.x < n_ship_ctas) {
-        cm::pdl_launch_dependents();
-        cm::ship_duty(ship, (int)blockIdx.x, n_ship_ctas);
-        return;
-    }
-    cm::pdl_launch_dependents();
-    const bool overlap = (flags & CM_SCORE_OVERLAP_PREVIOUS) != 0u;
-    if (!overlap) cm::pdl_wait();
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int b = ((int)blockIdx.x - n_ship_ctas) * WARPS + wid;
-    if (b >= n_guesses) return;
-    unsigned char *ring = bulk_smem + (size_t)wid * S * ROW_BYTES;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(bulk_smem + (size_t)WARPS * S * ROW_BYTES) + wid * S;
-
-    const int32_t *gi = guess_idx + (size_t)b * n_slots;
-    const bool is_exact = (exact != nullptr) && (exact[b] != 0);
-    int n = guess_len[b];
-    const int slot = answer_slot[b];
-    int32_t mine = (lane < n_slots) ? gi[lane] : -1;
-    if (lane == 0) {
-#pragma unroll
-        for (int i = 0; i < S; ++i) cm::mbar_init(bars + i, 1);
-        cm::fence_proxy_async();                    // make the initialised barriers visible to the copy engine
-    }
-    __syncwarp();
-    n = n < 0 ? 0 : (n > n_slots ? n_slots : n);
-    const bool slot_ok = slot >= 0 && slot < n_answers;
-    bool bad = (lane < n) && (mine < 0 || (int64_t)mine >= n_rows);
-    for (int c = 32 + lane; c < n; c += 32) {
-        const int32_t r = gi[c];
-        bad |= (r < 0) || ((int64_t)r >= n_rows);
-    }
-    bad = __any_sync(cm::kFullMask, bad) || n == 0 || !slot_ok;
-    const int n_live = (!is_exact && !bad) ? n : 0;
-
-    // prologue: the first S rows
-#pragma unroll
-    for (int k = 0; k < S; ++k) {
-        const int32_t r = __shfl_sync(cm::kFullMask, mine, k & 31);
-        if (lane == 0 && k < n_live) {
-            cm::mbar_expect_tx(bars + k, ROW_BYTES);
-            cm::bulk_g2s(ring + k * ROW_BYTES, table + (size_t)r * (DIM4 * 4), ROW_BYTES, bars + k);
-        }
-    }
-    float4 acc[VPL];
-#pragma unroll
-    for (int v = 0; v < VPL; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int k = 0; k < n_live; ++k) {
-        const int s_i = k % S;
-        cm::mbar_wait(bars + s_i, (uint32_t)((k / S) & 1));
-        const float4 *row = reinterpret_cast<const float4 *>(ring + s_i * ROW_BYTES);
-#pragma unroll
-        for (int v = 0; v < VPL; ++v) {
-            const int j = lane + 32 * v;
-            if (j < DIM4) {
-                const float4 x = row[j];
-                acc[v].x += x.x; acc[v].y += x.y; acc[v].z += x.z; acc[v].w += x.w;   // word order
-            }
-        }
-        // refill the slot with row k+S (indices beyond the first 32 are re-read from memory)
-        const int kn = k + S;
-        int32_t rn = __shfl_sync(cm::kFullMask, mine, kn & 31);
-        if (kn >= 32 && kn < n_live) rn = gi[kn];
-        __syncwarp();                                // every lane has read the slot
-        if (lane == 0 && kn < n_live) {
-            cm::fence_proxy_async();                 // generic-proxy reads before the async-proxy write
-            cm::mbar_expect_tx(bars + s_i, ROW_BYTES);
-            cm::bulk_g2s(ring + s_i * ROW_BYTES, table + (size_t)rn * (DIM4 * 4), ROW_BYTES, bars + s_i);
-        }
-    }
-    if (n_live > 1) {
-        const float fn = (float)n_live;
-#pragma unroll
-        for (int v = 0; v < VPL; ++v) {
-            acc[v].x = __fdiv_rn(acc[v].x, fn); acc[v].y = __fdiv_rn(acc[v].y, fn);
-            acc[v].z = __fdiv_rn(acc[v].z, fn); acc[v].w = __fdiv_rn(acc[v].w, fn);
-        }
-    }
-    if (overlap) cm::pdl_wait();
-    {
-        const int32_t ar = slot_ok ? ans_rows[slot] : -1;
-        bad = bad || ar < 0 || (int64_t)ar >= n_rows;
-    }
-    float p = 0.f;
-    if (n_live > 0) {
-        group_unitvec<VPL, 32>(acc);
-        const float4 *u = reinterpret_cast<const float4 *>(ans_unit) + (size_t)slot * DIM4;
-#pragma unroll
-        for (int v = 0; v < VPL; ++v) {
-            const int j = lane + 32 * v;
-            if (j < DIM4) {
-                const float4 q = u[j];
-                p = fmaf(acc[v].x, q.x, p); p = fmaf(acc[v].y, q.y, p);
-                p = fmaf(acc[v].z, q.z, p); p = fmaf(acc[v].w, q.w, p);
-            }
-        }
-        p = cm::warp_sum(p);
-    }
-    float result;
-    if (is_exact) result = 1.0f;
-    else if (bad) result = min_score;
-    else result = (p > min_score) ? p : min_score;
-    if (lane == 0) {
-        scores[b] = result;
-        if (centi != nullptr) centi[b] = (int32_t)floor((double)result * 10000.0 + 0.5);
-    }
-}
-
-// --------------------------------------------------------------------------------------
 // One-word guesses, many of them (more than one wave): a persistent, software-pipelined form of
 // the same arithmetic.  Each warp walks over groups of 32/LPG guesses; while the rows of the
 // current group are in flight it already loads the metadata (index, length, slot, exact flag) of
@@ -570,11 +439,15 @@ cm_score1_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
 
 namespace {
 
-// Kernel variants.  `CM_SCORE_VARIANT` (environment, read once) forces one for tuning runs.
-//   wide       : 32 lanes per guess, R rows per round   -- small phrase batches and any table width
-//   paired     : 16 lanes per guess, 2 guesses per warp -- bandwidth-bound phrase batches, dim 300
-//   single     : 8 lanes per guess, 4 guesses per warp  -- one-word guesses, dim 300
+// The four scoring kernels that ship for 300-d tables; each is the default for one class of shapes:
+//   wide       : 32 lanes per guess, 2 rows per round   -- small (latency-bound) phrase batches
+//   paired     : 16 lanes per guess, 2 guesses per warp -- bandwidth-bound phrase batches
+//   single     : 8 lanes per guess, 4 guesses per warp  -- one-word guesses (the reference's shape)
 //   persistent : the same with the next group's metadata prefetched -- very large one-word batches
+// Other table widths take the generic 32-lane kernel.  `CM_SCORE_KERNEL=wide|paired|single|persistent`
+// (environment, read once) overrides only the shape heuristic, for A/B timing of these four.
+enum ScoreKernel { kAuto = 0, kWide, kPaired, kSingle, kPersistent };
+
 template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE = false>
 void launch_variant(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
                     const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
@@ -627,38 +500,15 @@ void launch_single_persistent(const cm_engine *e, const int32_t *gi, const int32
     cm::count_launch();
 }
 
-template <int S, int THREADS, int MIN_BLOCKS>
-void launch_bulk(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
-                 const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
-                 int32_t *centi, uint32_t flags, cudaStream_t st, const cm::ShipArgs *ship) {
-    constexpr int WARPS = THREADS / 32;
-    const size_t smem = (size_t)WARPS * S * 1200 + (size_t)WARPS * S * 8;
-    if (smem > 48 * 1024)      // per device and cheap: no process-wide flag
-        cudaFuncSetAttribute(cm_score_bulk_kernel<S, THREADS, MIN_BLOCKS>,
-                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    const bool shipping = ship != nullptr && ship->world > 0;
-    const int n_ship_ctas = shipping ? cm::ship_ctas(ship->n) : 0;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)((B + WARPS - 1) / WARPS + n_ship_ctas));
-    cfg.blockDim = dim3(THREADS);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    cudaLaunchKernelEx(&cfg, cm_score_bulk_kernel<S, THREADS, MIN_BLOCKS>, (const float *)e->d_table, e->n_rows,
-                       gi, gl, B, N, (const float *)e->d_ans_unit, (const int32_t *)e->d_ans_rows,
-                       e->n_answers, slot, exact, min_score, scores, centi, flags, n_ship_ctas,
-                       shipping ? *ship : cm::ShipArgs{});
-    cm::count_launch();
-}
-
-int forced_variant() {
-    static const int v = [] {
-        const char *s = getenv("CM_SCORE_VARIANT");
-        return s ? atoi(s) : 0;
+ScoreKernel forced_kernel() {
+    static const ScoreKernel v = [] {
+        const char *s = getenv("CM_SCORE_KERNEL");
+        if (s == nullptr) return kAuto;
+        if (strcmp(s, "wide") == 0) return kWide;
+        if (strcmp(s, "paired") == 0) return kPaired;
+        if (strcmp(s, "single") == 0) return kSingle;
+        if (strcmp(s, "persistent") == 0) return kPersistent;
+        return kAuto;
     }();
     return v;
 }
@@ -673,31 +523,19 @@ void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int 
     launch_variant<VP, LPG, 1, STREAM, THREADS, MINB, true>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st, ship)
     if constexpr (VPL == 3) {
         if (e->dim == 300) {
-            int variant = forced_variant();
             // Measured on B200 (tools/probe_kernel.py, us per launch, CM_SCORE_OVERLAP_PREVIOUS):
-            //   4096x16 : wide R=2 12.9 | R=3 13.6 | R=4 13.9 (72 regs, spills) | R=8 43 (4 CTAs/SM)
-            //   65536x1 : 8-lane groups 15.5 | 16-lane 16.9 | 32-lane 23.9 | persistent 15.9
-            //   10^6 x1 : 8-lane groups 216  | persistent (80 regs, 6 CTAs/SM) 191 = 0.97 of peak
-            //   phrases : 16-lane groups (2 guesses per warp, 5 float4 per lane, R=1) beat 32-lane R=2 once
-            //             the launch is bandwidth-bound -- 4096x16 11.6 vs 12.9, 65536x16 181 vs 200,
-            //             16384x8 24.1 vs 30.4 -- and lose when it is latency-bound (512x8 6.0 vs 3.8)
-            if (variant == 0)
-                variant = (N == 1) ? (B > (1 << 18) ? 31 : 20) : ((int64_t)B * N >= 32768 ? 6 : 8);
-            if (variant >= 20 && variant < 40 && N != 1) variant = 8;
-            switch (variant) {
-                case 40: launch_bulk<4, 128, 8>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st, ship); return;
-                case 41: launch_bulk<6, 128, 7>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st, ship); return;
-                case 42: launch_bulk<8, 128, 5>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st, ship); return;
-                case 31: launch_single_persistent<10, 8, true, 128, 6>(e, gi, gl, B, slot, exact, min_score, scores, centi, flags, st, ship); return;
-                case 20: CM_S(8, true, 128, 8, 10); return;
-                case 23: CM_S(16, true, 128, 8, 5); return;
-                case 5: CM_V(16, 2, true, 128, 6, 5); return;
-                case 6: CM_V(16, 1, true, 128, 7, 5); return;
-                case 7: CM_V(8, 1, true, 128, 5, 10); return;
-                case 8: CM_V(32, 2, true, 128, 8, 3); return;
-                case 10: CM_V(32, 3, true, 128, 7, 3); return;
-                case 1: CM_V(32, 4, true, 128, 7, 3); return;
-                default: break;
+            //   4096x16 : wide 12.9 | paired 11.6;  65536x16 200 | 181;  16384x8 30.4 | 24.1;  512x8 3.8 | 6.0
+            //   65536x1 : single 15.5 | persistent 15.9;  10^6 x1 : single 216 | persistent 191
+            ScoreKernel k = forced_kernel();
+            if ((k == kSingle || k == kPersistent) && N != 1) k = kAuto;
+            if (k == kAuto)
+                k = (N == 1) ? (B > (1 << 18) ? kPersistent : kSingle)
+                             : ((int64_t)B * N >= 32768 ? kPaired : kWide);
+            switch (k) {
+                case kPersistent: launch_single_persistent<10, 8, true, 128, 6>(e, gi, gl, B, slot, exact, min_score, scores, centi, flags, st, ship); return;
+                case kSingle: CM_S(8, true, 128, 8, 10); return;
+                case kPaired: CM_V(16, 1, true, 128, 7, 5); return;
+                default: CM_V(32, 2, true, 128, 8, 3); return;
             }
         }
     }
@@ -1114,7 +952,11 @@ int cm_score_batch_host(cm_engine *e, const int32_t *guess_idx, const int32_t *g
 // In host code the name `g_noalloc_scratch` is only a handle for the symbol, not a device
 // address.  The address is looked up with cudaGetSymbolAddress once per device, with that
 // device current, the first time the entry point is used on it; make that first call before
-// any stream capture begins.
+// any stream capture begins.  That first call may also be the moment the CUDA runtime loads
+// this library's module onto the device (lazy loading), which allocates and synchronises inside
+// the driver: it belongs to start-up, not to the request path.  The address is cached for the
+// life of the process; cudaDeviceReset() invalidates it (and everything else the process holds
+// on that device), so a program that resets a device must not call this entry point on it again.
 // ======================================================================================
 static __device__ __align__(256) float g_noalloc_scratch[CM_NOALLOC_MAX_ANSWERS * CM_MAX_DIM];
 
@@ -1123,6 +965,26 @@ namespace {
 constexpr int kMaxDevices = 64;
 std::mutex g_noalloc_mu;
 float *g_noalloc_ptr[kMaxDevices] = {};
+
+bool g_noalloc_checked[kMaxDevices] = {};
+
+// Once per device: it exists and is an sm_100 part -- the checks cm_engine_create makes -- so
+// that a wrong ordinal is reported as such and not as a cudaSetDevice or launch error.
+int noalloc_check_device(int device) {
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_checked[device]) return CM_OK;
+    int n_dev = 0;
+    CM_CUDA(cudaGetDeviceCount(&n_dev));
+    if (device >= n_dev) return fail(CM_ERR_INVALID, "device %d not in [0, %d)", device, n_dev);
+    int major = 0, minor = 0;
+    CM_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+    CM_CUDA(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, device));
+    if (major != 10)
+        return fail(CM_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only",
+                    device, major, minor);
+    g_noalloc_checked[device] = true;
+    return CM_OK;
+}
 
 // Device address of the scratch array on `device` (which must be current).
 int noalloc_scratch_address(int device, float **out) {
@@ -1168,6 +1030,7 @@ extern "C" int cm_score_batch_noalloc(int device, const float *d_table, int64_t 
     if (!d_guess_idx || !d_guess_len || !d_answer_slot || !d_scores)
         return fail(CM_ERR_INVALID, "a required buffer pointer is NULL");
 
+    if (int rc = noalloc_check_device(device)) return rc;
     DeviceGuard guard(device);
     if (!guard.ok) return fail(CM_ERR_CUDA, "cudaSetDevice(%d) failed", device);
     float *scratch = nullptr;

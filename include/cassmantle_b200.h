@@ -286,11 +286,16 @@ int cm_gather_trace(cm_gather *g, unsigned long long *out512);   /* developer ai
  * The unit vectors of the answers live in one fixed array inside the library
  * (CM_NOALLOC_MAX_ANSWERS x CM_MAX_DIM floats = 256 KiB, resident on every GPU that loads the
  * library until the process exits); n_answers above CM_NOALLOC_MAX_ANSWERS or dim above
- * CM_MAX_DIM is rejected with CM_ERR_INVALID.  The call performs no cudaMalloc/cudaFree.
- * The first call on a device looks the array's address up (once per device): make that
- * first call before any stream capture.  All calls share the array and each rewrites the
- * part it uses, so calls that may overlap on the GPU (different streams, unordered) race --
- * keep them on one stream or order them.  Asynchronous on `stream`.                         */
+ * CM_MAX_DIM is rejected with CM_ERR_INVALID.  The call itself performs no cudaMalloc,
+ * cudaFree or other allocating routine.  The first call on a device checks the device and
+ * looks the array's address up (once per device): make that first call at start-up, before
+ * any stream capture -- with CUDA's lazy module loading it can also be the moment the runtime
+ * loads this library onto that device, which allocates and synchronises inside the driver.
+ * The address is then cached until the process exits: after cudaDeviceReset() on that device
+ * it is stale, so do not call this entry point on a device that has been reset.
+ * All calls share the array and each rewrites the part it uses, so calls that may overlap on
+ * the GPU (different streams, unordered) race -- keep them on one stream or order them.
+ * Asynchronous on `stream`.                                                                 */
 #define CM_NOALLOC_MAX_ANSWERS 64
 int cm_score_batch_noalloc(int device, const float *d_table, int64_t n_rows, int dim,
                            const int32_t *d_answer_rows, int n_answers,

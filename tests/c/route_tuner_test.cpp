@@ -78,6 +78,23 @@ int main() {
         drive(t, c, RouteTuner::kWarmSubmits + 2 * kTrial, 50e-6, 50e-6);
         CHECK(t.best_in_place());
     }
+    {   // idle gaps (bursty traffic) never decide a trial: a window that contains one starts again
+        RouteTuner t; double c = 0.0;
+        drive(t, c, RouteTuner::kWarmSubmits, 10e-6, 10e-6);
+        // in-place window with a long pause in the middle, copy window without: without the
+        // restart the copy engine would "win" by the length of the pause
+        drive(t, c, kTrial / 2, 10e-6, 10e-6);
+        c += 0.5;
+        CHECK(drive(t, c, kTrial, 10e-6, 10e-6) == kTrial);       // the in-place window ran again in full
+        CHECK(drive(t, c, kTrial, 10e-6, 10e-6) == 0);
+        CHECK(t.best_in_place());
+        CHECK(t.window_seconds(true) < 300e-5);
+        // a caller that pauses every 100 submits never finishes a trial and keeps its route
+        RouteTuner u; c = 0.0;
+        long in_place = 0;
+        for (int burst = 0; burst < 200; ++burst) { in_place += drive(u, c, 100, 10e-6, 5e-6); c += 0.01; }
+        CHECK(in_place == 200 * 100);
+    }
     {   // over a long run the losing route gets only the trial windows
         RouteTuner t; double c = 0.0;
         const long total = RouteTuner::kWarmSubmits + 5 * kCycle;

@@ -34,7 +34,9 @@ def test_matches_live_pillow(h, w, c, mode):
     rng = np.random.default_rng(h * 1000 + w)
     img = rng.integers(0, 256, (h, w, c), dtype=np.uint8)
     pil = Image.fromarray(img[..., 0] if c == 1 else img, mode)
-    radii = [0.0, 0.1, 0.5, 1.0, 2.5, 7.77, 14.9, 15.0, 40.0, 400.0] + list(rng.uniform(0, 15, 10))
+    # negative radii: Pillow squares the radius, and score_to_blur of a cosine that rounded to
+    # 1.0000001 is slightly negative in the reference (src/backend.py:319-320)
+    radii = [0.0, 0.1, 0.5, 1.0, 2.5, 7.77, 14.9, 15.0, 40.0, 400.0, -3.6e-6, -2.5] + list(rng.uniform(0, 15, 10))
     blur = ImageBlur(h, w, c, max_batch=7)                       # smaller than the batch: chunked
     blur.set_image(pil)
     got = blur.blur_radii(radii)
@@ -79,5 +81,7 @@ def test_blur_argument_errors():
         blur.set_image(np.zeros((33, 32, 3), np.uint8))
     blur.set_image(np.zeros((32, 32, 3), np.uint8))
     with pytest.raises(_lib.CassMantleError):
-        blur.blur_radii([-1.0])
+        blur.blur_radii([float("nan")])
+    with pytest.raises(_lib.CassMantleError):
+        blur.blur_radii([5000.0])
     blur.close()

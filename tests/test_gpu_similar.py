@@ -179,6 +179,5 @@ def test_opt_in_16_lane_scan_agrees_with_the_default():
     _compare_scans(50_000, [(5, 1), (77, 51), (4242, 1024)])
 
 
-@pytest.mark.xfail(reason="opt-in kernel (CM_SCAN16=1): its first run at 3,000,000 rows happens here", strict=False)
 def test_opt_in_16_lane_scan_at_full_size():
     _compare_scans(synth.FULL_ROWS, [(2_718_281, 51), (7, 200)])
