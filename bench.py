@@ -9,16 +9,27 @@ download_model.py:9), 2 hidden words per round (src/backend.py:49), ~5 % unknown
 ~1 % exact matches.  Data are synthetic (cassmantle_b200/synth.py): no weights exist offline.
 
 A step = one pass of the hot path over one batch = one launch of cm_score_kernel.
-  value  : device-resident inputs, K steps timed with CUDA events on the launch stream,
-           max over ranks.  A ring of distinct batches is cycled so consecutive steps touch
-           different table rows (uniform over 3.6 GB >> 126 MB of L2).
+  value  : device-resident inputs, K steps enqueued by ONE C-ABI call per ring of batches
+           (cm_score_batch_list_device), timed with CUDA events on the launch stream, max over
+           ranks.  A ring of distinct batches is cycled so consecutive steps touch different
+           table rows (uniform over 3.6 GB >> 126 MB of L2).  `sustained` repeats the measurement
+           over at least --min-wall-s of device time (a 20-step region is 0.25 ms).
   e2e    : the same K steps through the C-ABI host path (cm_pipe_*): inputs in page-locked
-           host memory -> H2D DMA -> kernel -> scores back in host memory, 4 batches in flight;
+           host memory -> PCIe -> kernel -> scores back in host memory, 8 batches in flight;
            the blocking one-call-per-step figure (cm_score_batch_host) is reported beside it.
   roofline : the scoring kernel alone, >= 1 s of back-to-back launches timed with CUDA events;
-           achieved = algorithmic bytes (N*1204 + 8 per guess) / time.
+           achieved = the bytes the timed batches REQUIRE / time: 1200 B for every row of a live
+           guess (an unknown word, an exact match or an unknown answer reads no rows, as in
+           src/backend.py:303-310) + 4 B per index + 8 B of length/slot/score per guess.
+           SURVEY.md 8(d)'s formula, which charges every guess N rows, is reported beside it
+           (`frac_survey_formula`), and `all_live_leg` times batches with no unknown words and no
+           exact matches, where the two coincide.
   cpu_baseline : the oracle's faithful per-pair port of src/backend.py:303-317 (what the
            reference does) on this box's cores, bounded sample; rank 0, N = 1 only.
+  N > 1  : weak scaling of the metric shape (every rank scores its own 4096x16 batch, scores of
+           every step all-gathered by the ship CTA riding in the next launch), the gathered
+           buffers verified on steps sampled through a separate run, plus BASELINE configs[3]
+           and [4] sharded (strong scaling) in `other_shapes`.
 
 `--impl reference` times that same CPU port alone, on the same config (the reference
 itself cannot run here: gensim is not installed and its weights cannot be downloaded).
@@ -26,7 +37,9 @@ itself cannot run here: gensim is not installed and its weights cannot be downlo
 from __future__ import annotations
 
 import argparse
+import ctypes
 import json
+import math
 import os
 import sys
 import threading
@@ -44,14 +57,38 @@ V, D = synth.FULL_ROWS, synth.DIM
 B, N = 4096, 16
 N_ANSWERS = 2
 MIN_SCORE = 0.01
-RING = 64                      # distinct batches cycled through (64 x 79 MB of rows)
+RING = 64                      # distinct batches cycled through (64 x 74 MB of rows)
 OVERLAP = 1                    # CM_SCORE_OVERLAP_PREVIOUS: the ring's batches are independent
 PIPE_DEPTH = 8                 # batches in flight on the pipelined host path
-BYTES_PER_GUESS = N * (D * 4 + 4) + 8      # N rows + N indices + len/slot + score
+PIPE_PER_CALL = 4              # steps fed per cm_pipe_cycle_many call
+GATHER_DEPTH = 8
 METRIC = "guesses_scored_per_sec"
 UNIT = "guesses/s"
 WORKLOAD = (f"{B} guesses x {N} word slots per step, resident table {V}x{D} fp32 (3.6 GB), "
             f"{N_ANSWERS} answers, 5% OOV, 1% exact; BASELINE.json configs[2]")
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "traffic.json")
+
+
+def live_rows(idx, ln, slot, ex, ans, n_rows: int = V) -> int:
+    """Table rows a batch makes the kernel read: the used slots of every guess that is neither an
+    exact match nor a KeyError (unknown word, empty guess, bad slot, unknown answer) --
+    src/backend.py:305-309, cm_scorer.cu score_groups `active`."""
+    n_slots = idx.shape[1]
+    n = np.clip(ln, 0, n_slots)
+    used = np.arange(n_slots)[None, :] < n[:, None]
+    bad = (((idx < 0) | (idx >= n_rows)) & used).any(axis=1) | (n == 0)
+    slot_ok = (slot >= 0) & (slot < len(ans))
+    bad |= ~slot_ok | (np.asarray(ans)[np.where(slot_ok, slot, 0)] < 0)
+    live = ~bad & (np.zeros(len(n), bool) if ex is None else ~ex.astype(bool))
+    return int(n[live].sum())
+
+
+def required_bytes(rows: int, n_guesses: int, n_slots: int) -> int:
+    return rows * D * 4 + n_guesses * (n_slots * 4 + 8)
+
+
+def survey_bytes(n_guesses: int, n_slots: int) -> int:
+    return n_guesses * (n_slots * (D * 4 + 4) + 8)           # SURVEY.md 8(d): B * (N*1204 + 8)
 
 
 def make_ring(seed0: int):
@@ -223,6 +260,36 @@ def bind_near_gpu(local_rank: int):
 # ------------------------------------------------------------------------------------------
 # own arm
 # ------------------------------------------------------------------------------------------
+class BatchList:
+    """A ctypes array of cm_batch over device buffers, passed to cm_score_batch_list_device in
+    windows: one boundary crossing enqueues up to len(ring) launches (keeps Python out of the
+    timed loop)."""
+
+    def __init__(self, lib, cm_batch, eng_h, gather_h, ptrs, n_guesses, n_slots, out_ptr, st):
+        self.lib, self.eng_h, self.gather_h, self.st = lib, eng_h, gather_h, st
+        self.n = len(ptrs)
+        self.arr = (cm_batch * (2 * self.n))()
+        for k in range(2 * self.n):
+            q = ptrs[k % self.n]
+            self.arr[k] = cm_batch(q[0], q[1], q[2], q[3], out_ptr, None, n_guesses, n_slots)
+        self.stride = ctypes.sizeof(cm_batch)
+        self.ms = ctypes.c_float(np.float32(MIN_SCORE))
+        self.fn = lib.cm_score_batch_list_device
+
+    def run(self, first: int, count: int) -> None:
+        """Enqueue steps first .. first+count-1 (step i uses ring batch i % n)."""
+        i = first
+        end = first + count
+        while i < end:
+            k = min(self.n, end - i)
+            rc = self.fn(self.eng_h, self.gather_h, ctypes.byref(self.arr, (i % self.n) * self.stride), k,
+                         self.ms, OVERLAP, self.st)
+            if rc != 0:
+                from cassmantle_b200 import _lib
+                _lib.check(rc)
+            i += k
+
+
 def run_own(args) -> None:
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -274,6 +341,7 @@ def run_own(args) -> None:
     import torch.distributed as dist
 
     from cassmantle_b200 import _lib
+    from cassmantle_b200.dist import ScoreGather, shard_bounds
     from cassmantle_b200.engine import ScoringEngine
 
     torch.cuda.set_device(local_rank)
@@ -291,6 +359,7 @@ def run_own(args) -> None:
     for idx, ln, slot, ex in ring:
         d_ring.append(tuple(torch.from_numpy(a).to(dev) for a in (idx, ln, slot, ex)))
         h_ring.append(tuple(torch.from_numpy(a).pin_memory() for a in (idx, ln, slot, ex)))
+    ring_rows = [live_rows(idx, ln, slot, ex, ans) for idx, ln, slot, ex in ring]
     d_scores = torch.empty(B, dtype=torch.float32, device=dev)
     gathered = torch.empty(world * B, dtype=torch.float32, device=dev) if world > 1 else None
     h_scores = torch.empty(B, dtype=torch.float32).pin_memory()
@@ -299,43 +368,46 @@ def run_own(args) -> None:
     st = stream.cuda_stream
     assert st != 0
 
-    gather = None
-    if world > 1 and args.collective == "fused":
-        # peer mappings need CUDA IPC between the ranks' processes; if any rank cannot set them up
-        # (a sandbox without IPC) every rank falls back to the NCCL all-gather and says so
-        from cassmantle_b200.dist import ScoreGather
-        ok_local = 1.0
+    def open_gather(max_per_rank: int):
+        """Peer mappings need CUDA IPC between the ranks' processes; if any rank cannot set them up
+        (a sandbox without IPC) every rank gets None and the caller falls back / skips."""
+        g, ok_local = None, 1.0
         try:
-            gather = ScoreGather(eng, B, depth=8)
-            gather.exchange_handles()
+            g = ScoreGather(eng, max_per_rank, depth=GATHER_DEPTH)
+            g.exchange_handles()
         except Exception as exc:      # noqa: BLE001
-            print(f"[bench] rank {rank}: peer-memory gather unavailable ({exc}); using NCCL", file=sys.stderr)
+            print(f"[bench] rank {rank}: peer-memory gather unavailable ({exc})", file=sys.stderr)
             ok_local = 0.0
         t_ok = torch.tensor([ok_local], device=dev)
         dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
         if t_ok.item() != 1.0:
-            if gather is not None:
-                gather.close()
-            gather = None
+            if g is not None:
+                g.close()
+            g = None
         dist.barrier()
+        return g
 
-    import ctypes
+    gather = open_gather(B) if (world > 1 and args.collective == "fused") else None
+
     ms32 = ctypes.c_float(np.float32(MIN_SCORE))
     t_ring = [(t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(), t[3].data_ptr()) for t in d_ring]
-    score_dev, score_gather = lib.cm_score_batch_device, lib.cm_score_batch_gather
+    score_dev = lib.cm_score_batch_device
     eh, out_p = eng._h, d_scores.data_ptr()
     gh = gather._h if gather is not None else None
+    steps_list = BatchList(lib, _lib.cm_batch, eh, gh, t_ring, B, N, out_p, st)      # the timed path
+    kernel_list = steps_list if gh is None else BatchList(lib, _lib.cm_batch, eh, None, t_ring, B, N, out_p, st)
+    nccl_path = world > 1 and gather is None
 
-    def step_device(i: int) -> None:        # the raw C-ABI calls: keep Python out of the timed loop
-        p = t_ring[i % RING]
-        if gh is not None:   # scoring launch + exchange kernel: every rank ends up with all scores
-            rc = score_gather(eh, gh, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
-        else:
-            rc = score_dev(eh, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
-            if world > 1:    # --collective nccl: a separate all-gather per step
-                dist.all_gather_into_tensor(gathered, d_scores)
-        if rc != 0:
-            _lib.check(rc)
+    def run_steps(first: int, count: int) -> None:
+        if not nccl_path:
+            steps_list.run(first, count)        # one C-ABI call per <= RING steps
+            return
+        for i in range(first, first + count):   # --collective nccl: a separate all-gather per step
+            q = t_ring[i % RING]
+            rc = score_dev(eh, q[0], q[1], B, N, q[2], q[3], ms32, out_p, None, OVERLAP, st)
+            if rc != 0:
+                _lib.check(rc)
+            dist.all_gather_into_tensor(gathered, d_scores)
 
     h_np = [tuple(t.numpy() for t in tup) for tup in h_ring]
     h_scores_np = h_scores.numpy()
@@ -360,6 +432,87 @@ def run_own(args) -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def timed_steps(first: int, count: int):
+        """`count` steps between two events on the launch stream, a barrier + synchronize on both
+        sides; returns (device ms, max over ranks; host seconds spent enqueueing)."""
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        t_h = time.perf_counter()
+        run_steps(first, count)
+        e1.record(stream)
+        t_h = time.perf_counter() - t_h
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1)), t_h
+
+    # ---- gather verification: which steps, and what every rank's scores must be -------------
+    expected_cache = {}
+
+    def expected_scores(r: int, bi: int) -> np.ndarray:
+        """Scores of ring batch `bi` of rank `r` (rings are seeded by rank), re-scored locally."""
+        if (r, bi) not in expected_cache:
+            if r not in expected_cache:
+                expected_cache[r] = ring if r == rank else make_ring(1000 + 7919 * r)[1]
+            idx_r, ln_r, slot_r, ex_r = expected_cache[r][bi]
+            expected_cache[(r, bi)] = eng.score_host(idx_r, ln_r, slot_r, ex_r, MIN_SCORE)[0]
+        return expected_cache[(r, bi)]
+
+    def verify_gather_run(first: int, count: int):
+        """An untimed run of `count` gathered steps in which the receive buffers are read back on
+        every 97th step and on the last GATHER_DEPTH + 1 steps: at such a step the stream waits for
+        all ranks (cm_gather_wait, the consumer's call), then BOTH the buffer of that step (shipped
+        by the stand-alone kernel of the wait) and the buffer of the step before it (shipped by the
+        CTA riding in this step's scoring launch) are copied out.  Compared bit for bit afterwards
+        with a local re-score of every rank's batch of that step."""
+        sample = sorted({j for j in range(first, first + count) if (j - first) % 97 == 96}
+                        | set(range(max(first + 1, first + count - GATHER_DEPTH - 1), first + count)))
+        buf_floats = world * gather.stride
+        host = torch.empty((2 * len(sample), buf_floats), dtype=torch.float32).pin_memory()
+        block = gather.block_ptr()
+        taken, k, prev = [], 0, first
+        for j in sample:
+            steps_list.run(prev, j + 1 - prev)
+            prev = j + 1
+            ptr = gather.wait(st)
+            slot_j = (ptr - block) // (buf_floats * 4)
+            ptr_before = block + ((slot_j - 1) % GATHER_DEPTH) * buf_floats * 4
+            host[k].copy_(gather.as_tensor(ptr).reshape(-1), non_blocking=True)
+            host[k + 1].copy_(gather.as_tensor(ptr_before).reshape(-1), non_blocking=True)
+            taken.append((j, k))
+            k += 2
+        steps_list.run(prev, first + count - prev)
+        gather.wait(st)
+        torch.cuda.synchronize()
+        ok = gather.timed_out() == 0
+        got = host.numpy().reshape(2 * len(sample), world, gather.stride)
+        verified = set()
+        for j, k in taken:
+            for step, row in ((j, k), (j - 1, k + 1)):
+                for r in range(world):
+                    want_r = expected_scores(r, step % RING)
+                    ok = ok and bool(np.array_equal(got[row, r, :B].view(np.uint32), want_r.view(np.uint32)))
+                verified.add(step)
+        t_ok = torch.tensor([1.0 if ok else 0.0], device=dev)
+        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+        return bool(t_ok.item() == 1.0), len(verified)
+
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        with open(peaks_path) as f:
+            peak, peak_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+
+    def kernel_time_us(blist: BatchList, n_launch: int, warm: int = 50) -> float:
+        blist.run(0, warm)
+        torch.cuda.synchronize()
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r0.record(stream)
+        blist.run(0, n_launch)
+        r1.record(stream)
+        torch.cuda.synchronize()
+        return r0.elapsed_time(r1) * 1e3 / n_launch
+
     # The timed phases run once; if the clock record shows a thermal / hardware slowdown they are
     # run a second time and that measurement is the one reported (sw_power_cap is only noted).
     pipe = None
@@ -368,36 +521,23 @@ def run_own(args) -> None:
         sampler.start()
 
         # ---- value: device-resident, K steps ------------------------------------------------
-        for i in range(args.warmup):
-            step_device(i)
-        barrier()
+        run_steps(0, args.warmup)
         launches0 = lib.cm_kernel_launch_count()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        t_enq = time.perf_counter()
-        for i in range(args.steps):
-            step_device(args.warmup + i)
-        e1.record(stream)
-        t_enq = time.perf_counter() - t_enq
-        barrier()
+        dev_ms, t_enq = timed_steps(args.warmup, args.steps)
         gpu_launches = int(lib.cm_kernel_launch_count() - launches0)
-        dev_ms = max_over_ranks(e0.elapsed_time(e1))
         value = args.steps * B * world / (dev_ms * 1e-3)
+        # the same over at least --min-wall-s of device time
+        n_long = int(min(400_000, max(args.steps, math.ceil(args.min_wall_s * 1e3 / max(dev_ms / args.steps, 1e-3)))))
+        long_ms, _ = timed_steps(args.warmup + args.steps, n_long)
+        sustained = {"value": n_long * B * world / (long_ms * 1e-3), "unit": UNIT, "steps": n_long,
+                     "ms_per_step": long_ms / n_long}
 
-        # every rank must now hold every rank's scores of the last step (checked against a local
-        # re-score of the peers' batches, which are seeded by rank)
-        gather_check = None
+        # every rank must hold every rank's scores, on steps spread through a run
+        gather_check, gather_steps = None, 0
         if gather is not None:
-            ptr = gather.wait(st)          # ships the last step (no launch follows it) and waits for all ranks
+            gather.wait(st)
             torch.cuda.synchronize()
-            got = gather.as_tensor(ptr).cpu().numpy()
-            last = (args.warmup + args.steps - 1) % RING
-            ok = gather.timed_out() == 0
-            for r in range(world):
-                _, ring_r = make_ring(1000 + 7919 * r)
-                idx_r, ln_r, slot_r, ex_r = ring_r[last]
-                want_r, _ = eng.score_host(idx_r, ln_r, slot_r, ex_r, MIN_SCORE)
-                ok = ok and bool(np.array_equal(got[r, :B].view(np.uint32), want_r.view(np.uint32)))
+            gather_check, gather_steps = verify_gather_run(0, max(200, min(args.steps, 2000)))
             if os.environ.get("CM_GATHER_TRACE") and rank == 0:
                 tr = np.zeros(512, dtype=np.uint64)
                 lib.cm_gather_trace(gather._h, tr.ctypes.data)
@@ -407,37 +547,48 @@ def run_own(args) -> None:
                     b0 = int(row[1])
                     print("trace step", int(row[0]), "start", b0 % 10**9, "order", int(row[2]) - b0, "stores", int(row[3]) - b0,
                           "fence", int(row[4]) - b0, "flags", int(row[5]) - b0, "peers", int(row[6]) - b0, file=sys.stderr)
-            t_ok = torch.tensor([1.0 if ok else 0.0], device=dev)
-            dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
-            gather_check = bool(t_ok.item() == 1.0)
 
         # ---- roofline: the scoring kernel alone, >= ~1 s of launches -------------------------
         per_step_ms = max(dev_ms / args.steps, 1e-3)
         n_roof = int(min(200_000, max(2000, args.roofline_s * 1e3 / per_step_ms)))
-        fn, h = lib.cm_score_batch_device, eng._h
-        for i in range(50):
-            p = t_ring[i % RING]
-            fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
-        torch.cuda.synchronize()
-        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        r0.record(stream)
-        for i in range(n_roof):
-            p = t_ring[i % RING]
-            fn(h, p[0], p[1], B, N, p[2], p[3], ms32, out_p, None, OVERLAP, st)
-        r1.record(stream)
-        torch.cuda.synchronize()
-        kern_us = r0.elapsed_time(r1) * 1e3 / n_roof
-        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-        if os.path.exists(peaks_path):
-            with open(peaks_path) as f:
-                peak, peak_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
-        else:
-            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-        achieved = B * BYTES_PER_GUESS / (kern_us * 1e-6) / 1e9
+        kern_us = kernel_time_us(kernel_list, n_roof)
+        # launch i used ring batch i % RING: the bytes those launches needed, averaged per launch
+        visits = np.bincount(np.arange(n_roof) % RING, minlength=RING)
+        rows_per_launch = float(np.dot(visits, ring_rows)) / n_roof
+        need = rows_per_launch * D * 4 + B * (N * 4 + 8)
+        achieved = need / (kern_us * 1e-6) / 1e9
+        survey = survey_bytes(B, N) / (kern_us * 1e-6) / 1e9
+        traffic, traffic_src = None, None
+        if os.path.exists(TRAFFIC_FILE):           # per-launch DRAM bytes of this kernel from the committed ncu capture
+            with open(TRAFFIC_FILE) as f:
+                tj = json.load(f)
+            traffic, traffic_src = tj.get("dram_bytes_per_launch"), tj.get("source")
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                    "frac": achieved / peak, "traffic": TRAFFIC_BYTES_PER_LAUNCH,
-                    "kernel": "cm_score_kernel<VPL=5,LPG=16,R=1> (4096x16 launches, CM_SCORE_OVERLAP_PREVIOUS)", "kernel_us": kern_us, "launches_timed": n_roof,
-                    "algorithmic_bytes_per_launch": B * BYTES_PER_GUESS, "peak_source": peak_src}
+                    "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                    "kernel": "cm_score_kernel<VPL=5,LPG=16,R=1> (4096x16 launches, CM_SCORE_OVERLAP_PREVIOUS)",
+                    "kernel_us": kern_us, "launches_timed": n_roof,
+                    "algorithmic_bytes_per_launch": need,
+                    "bytes_model": "1200 B x rows of live guesses (no rows for unknown words, exact matches, unknown "
+                                   "answers) + 4 B per index + 8 B of length/slot/score per guess",
+                    "live_rows_per_launch": rows_per_launch, "live_row_share": rows_per_launch / (B * N),
+                    "frac_survey_formula": survey / peak, "survey_formula_bytes_per_launch": survey_bytes(B, N),
+                    "peak_source": peak_src}
+        # the same kernel on batches with no unknown words and no exact matches: both models agree
+        if rank == 0 and not args.no_other_shapes:
+            live_bufs, live_total = [], 0
+            for i in range(16):
+                idx2, ln2, _, slot2, ex2 = synth.make_guess_batch(B, N, V, N_ANSWERS, seed=9000 + i, near_frac=0.0,
+                                                                  oov_frac=0.0, exact_frac=0.0)
+                live_total += live_rows(idx2, ln2, slot2, ex2, ans)
+                live_bufs.append([torch.from_numpy(a).to(dev) for a in (idx2, ln2, slot2, ex2)])
+            assert live_total == 16 * B * N
+            ll = BatchList(lib, _lib.cm_batch, eh, None, [tuple(t.data_ptr() for t in q) for q in live_bufs],
+                           B, N, out_p, st)
+            live_us = kernel_time_us(ll, max(2000, n_roof // 4))
+            roofline["all_live_leg"] = {"kernel_us": live_us, "achieved": survey_bytes(B, N) / (live_us * 1e-6) / 1e9,
+                                        "frac": survey_bytes(B, N) / (live_us * 1e-6) / 1e9 / peak,
+                                        "note": "oov_frac = exact_frac = 0: every guess reads its 16 rows"}
+            del live_bufs, ll
 
         # ---- e2e: host buffers through the C ABI ---------------------------------------------
         # (a) pipelined: cm_pipe_* with PIPE_DEPTH batches in flight.  The ring's batches live in
@@ -445,9 +596,10 @@ def run_own(args) -> None:
         #     step moves that step's inputs across PCIe to the GPU (at this batch size the scoring
         #     kernel reads them from the slot itself; the copy-engine route is timed beside it),
         #     scores them, and the step's scores land back in page-locked host memory, where the
-        #     host reads them.
+        #     host reads them.  The producer hands PIPE_PER_CALL steps to one cm_pipe_cycle_many call.
         # (b) synchronous: one cm_score_batch_host call per step (what Backend.compute_scores uses).
         from cassmantle_b200.engine import ScoringPipe
+
         def make_pipe():
             pp = ScoringPipe(eng, depth=RING, max_guesses=B, max_slots=N)
             vv = []
@@ -468,34 +620,51 @@ def run_own(args) -> None:
             os.environ["CM_PIPE_ROUTE"] = "inplace"       # the kernel reads/writes the pinned slot itself
             pipe_inp, views_inp = make_pipe()
             del os.environ["CM_PIPE_ROUTE"]
-        submit, wait, cycle, ph = lib.cm_pipe_submit, lib.cm_pipe_wait, lib.cm_pipe_cycle, pipe._h
+        submit, wait, cycle, many, ph = (lib.cm_pipe_submit, lib.cm_pipe_wait, lib.cm_pipe_cycle,
+                                         lib.cm_pipe_cycle_many, pipe._h)
         all_views = views
         checksum = 0.0
 
-        def run_pipe(first: int, count: int, fill: bool = False) -> None:
+        def run_pipe(first: int, count: int, fill: bool = False, per_call: int = PIPE_PER_CALL) -> None:
+            """Steps first .. first+count-1 through the pipe, PIPE_DEPTH in flight; step i lives in
+            slot i % RING.  per_call steps are handed over per boundary crossing."""
             nonlocal checksum
             views = all_views
-            for i in range(first, first + count):
-                if not fill and i - first >= PIPE_DEPTH:               # steady state: one call per step
-                    j = (i - PIPE_DEPTH) % RING
-                    if cycle(ph, j, i % RING, ms32, 0) != 0:
-                        _lib.check(-1)
-                    checksum += float(views[j]["scores"][0])       # the host consumes the result
+            i, end = first, first + count
+            while i < end:
+                k = min(per_call, end - i)
+                w = i - PIPE_DEPTH                   # oldest step in flight
+                if fill:         # a producer that has its batches elsewhere in host memory copies them in
+                    for q in range(i, i + k):
+                        if q - PIPE_DEPTH >= first:
+                            wait(ph, (q - PIPE_DEPTH) % RING)
+                            checksum += float(views[(q - PIPE_DEPTH) % RING]["scores"][0])
+                        src, dst = h_np[(q + 1) % RING], views[q % RING]
+                        np.copyto(dst["guess_idx"], src[0]); np.copyto(dst["guess_len"], src[1])
+                        np.copyto(dst["answer_slot"], src[2]); np.copyto(dst["exact"], src[3])
+                        if submit(ph, q % RING, ms32, 0) != 0:
+                            _lib.check(-1)
+                    i += k
                     continue
-                if i - first >= PIPE_DEPTH:
-                    j = (i - PIPE_DEPTH) % RING
-                    wait(ph, j)
-                    checksum += float(views[j]["scores"][0])
-                if fill:         # a producer that has its batch elsewhere in host memory copies it in
-                    src, dst = h_np[(i + 1) % RING], views[i % RING]
-                    np.copyto(dst["guess_idx"], src[0]); np.copyto(dst["guess_len"], src[1])
-                    np.copyto(dst["answer_slot"], src[2]); np.copyto(dst["exact"], src[3])
-                if submit(ph, i % RING, ms32, 0) != 0:
+                if w >= first and k == 1:
+                    rc = cycle(ph, w % RING, i % RING, ms32, 0)
+                elif w >= first:
+                    rc = many(ph, w % RING, i % RING, k, ms32, 0)
+                else:                                # pipeline fill: nothing to wait for yet
+                    k = min(k, first + PIPE_DEPTH - i)
+                    rc = many(ph, -1, i % RING, k, ms32, 0)
+                if rc != 0:
+                    _lib.check(rc)
+                if w >= first:
+                    for q in range(w, w + k):
+                        checksum += float(views[q % RING]["scores"][0])   # the host consumes the results
+                i += k
+            lo = max(first, end - PIPE_DEPTH)
+            if end > lo:
+                if many(ph, lo % RING, -1, end - lo, ms32, 0) != 0:
                     _lib.check(-1)
-            for i in range(max(first, first + count - PIPE_DEPTH), first + count):
-                j = i % RING
-                wait(ph, j)
-                checksum += float(views[j]["scores"][0])
+                for q in range(lo, end):
+                    checksum += float(views[q % RING]["scores"][0])
 
         # untimed: the usual warm-up plus the pipe's own route trial (64 + 2 x 288 submits), so that
         # the timed steps run on the route it settled on, as a long-running server's would
@@ -511,10 +680,27 @@ def run_own(args) -> None:
         e2e = {"value": args.steps * B * world / e2e_s, "unit": UNIT,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 4,
                "ms_per_step": e2e_s / args.steps * 1e3, "gpu_launches": e2e_launches, "warmup_steps": pipe_warmup,
-               "api": f"cm_pipe_cycle = cm_pipe_wait + cm_pipe_submit (C ABI), {PIPE_DEPTH} batches in flight; each step's "
+               "steps_per_call": PIPE_PER_CALL,
+               "api": f"cm_pipe_cycle_many (C ABI): {PIPE_PER_CALL} x (cm_pipe_wait + cm_pipe_submit) per call, "
+                      f"{PIPE_DEPTH} batches in flight; each step's "
                       f"inputs cross PCIe from a page-locked host slot and its scores land back in it -- either read "
                       f"and written by the scoring kernel itself or moved by the copy engine, whichever the pipe "
-                      f"measures to be faster as it runs (both pinned routes are timed below)"}
+                      f"measures to be faster as it runs (both pinned routes are timed below); the timed region "
+                      f"includes the pipeline's fill and drain"}
+        # the same over at least --min-wall-s of wall time (K = 20 is 8 steps of fill + 8 of drain)
+        n_long_e = int(min(200_000, max(args.steps, math.ceil(args.min_wall_s / max(e2e_s / args.steps, 1e-6)))))
+        barrier()
+        t0 = time.perf_counter()
+        run_pipe(args.warmup, n_long_e)
+        long_s = max_over_ranks(time.perf_counter() - t0)
+        e2e["sustained"] = {"value": n_long_e * B * world / long_s, "unit": UNIT, "steps": n_long_e,
+                            "ms_per_step": long_s / n_long_e * 1e3}
+        barrier()
+        t0 = time.perf_counter()
+        run_pipe(args.warmup, n_long_e, per_call=1)
+        one_s = max_over_ranks(time.perf_counter() - t0)
+        e2e["one_step_per_call"] = {"value": n_long_e * B * world / one_s, "unit": UNIT, "steps": n_long_e,
+                                    "ms_per_step": one_s / n_long_e * 1e3, "api": "cm_pipe_cycle, one call per step"}
         # (a'') the same call pinned to each route (the pipe itself times both as it runs and keeps
         #       the faster one: which one wins depends on how busy the PCIe path is)
         for tag, pp, vv, note in (("copy_engine_route", pipe_dma, views_dma, "CM_PIPE_ROUTE=copy: H2D DMA, kernel, D2H DMA per step"),
@@ -523,15 +709,16 @@ def run_own(args) -> None:
             run_pipe(0, max(args.warmup, PIPE_DEPTH))
             barrier()
             t0 = time.perf_counter()
-            run_pipe(args.warmup, args.steps)
+            run_pipe(args.warmup, n_long_e)
             r_s = max_over_ranks(time.perf_counter() - t0)
-            e2e[tag] = {"value": args.steps * B * world / r_s, "unit": UNIT, "ms_per_step": r_s / args.steps * 1e3, "note": note}
+            e2e[tag] = {"value": n_long_e * B * world / r_s, "unit": UNIT, "steps": n_long_e,
+                        "ms_per_step": r_s / n_long_e * 1e3, "note": note}
             for j in range(2):
                 assert np.array_equal(np.asarray(vv[j]["scores"]).view(np.uint32),
                                       np.asarray(views[j]["scores"]).view(np.uint32))
         ph, all_views = pipe._h, views
         # (a') the same with the producer's copy into the slot inside the timed region
-        n_fill = min(args.steps, 1000)
+        n_fill = min(max(args.steps, 200), 1000)
         run_pipe(0, PIPE_DEPTH, fill=True)
         t0 = time.perf_counter()
         run_pipe(7, n_fill, fill=True)
@@ -546,7 +733,7 @@ def run_own(args) -> None:
             step_host(i)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        n_sync = min(args.steps, 2000)
+        n_sync = min(max(args.steps, 200), 2000)
         for i in range(n_sync):
             step_host(args.warmup + i)
         sync_s = time.perf_counter() - t0
@@ -563,6 +750,17 @@ def run_own(args) -> None:
         if not (set(timed_clocks["reasons"]) & set(ClockSampler.BAD)):
             break
 
+    def time_shape(ptr2, b2, n2, out_ptr, reps, g_h=None):
+        bl = BatchList(lib, _lib.cm_batch, eh, g_h, ptr2, b2, n2, out_ptr, st)
+        bl.run(0, 10)
+        torch.cuda.synchronize()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record(stream)
+        bl.run(0, reps)
+        s1.record(stream)
+        torch.cuda.synchronize()
+        return s0.elapsed_time(s1) * 1e3 / reps, bl
+
     # ---- the other BASELINE.json shapes, kernel only (N = 1 is the only shape
     #      the reference itself produces; the seq-N shapes are the labelled mean-pool extension)
     other = None
@@ -575,41 +773,30 @@ def run_own(args) -> None:
                               (16384, 64, "configs[4] long-guess stress"),
                               (4096, 16, "metric shape with Zipf(1.0) word frequencies instead of uniform rows")]:
             k_ring = 8
-            bufs = []
+            bufs, rows2 = [], 0
             for i in range(k_ring):
                 idx2, ln2, _, slot2, ex2 = synth.make_guess_batch(b2, n2, V, N_ANSWERS, seed=7000 + i, near_frac=0.0)
                 if "Zipf" in tag:        # realistic traffic: rank r drawn with p ~ 1/r
                     zr = np.random.default_rng(7100 + i)
                     z = np.minimum(np.exp(zr.random(idx2.shape) * np.log(V)).astype(np.int64) - 1, V - 1)
                     idx2 = np.where(idx2 >= 0, z, -1).astype(np.int32)
+                rows2 += live_rows(idx2, ln2, slot2, ex2, ans)
                 bufs.append([torch.from_numpy(a).to(dev) for a in (idx2, ln2, slot2, ex2)])
             out2 = torch.empty(b2, dtype=torch.float32, device=dev)
             ptr2 = [(q[0].data_ptr(), q[1].data_ptr(), q[2].data_ptr(), q[3].data_ptr()) for q in bufs]
-            reps = 300 if b2 * n2 < 500_000 else 60
-            for i in range(10):
-                q = ptr2[i % k_ring]
-                fn(h, q[0], q[1], b2, n2, q[2], q[3], ms32, out2.data_ptr(), None, OVERLAP, st)
-            torch.cuda.synchronize()
-            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            s0.record(stream)
-            for i in range(reps):
-                q = ptr2[i % k_ring]
-                fn(h, q[0], q[1], b2, n2, q[2], q[3], ms32, out2.data_ptr(), None, OVERLAP, st)
-            s1.record(stream)
-            torch.cuda.synchronize()
-            us2 = s0.elapsed_time(s1) * 1e3 / reps
-            alg = b2 * (n2 * (D * 4 + 4) + 8)
+            reps = 320 if b2 * n2 < 500_000 else 64          # multiples of k_ring: every batch equally often
+            us2, bl2 = time_shape(ptr2, b2, n2, out2.data_ptr(), reps)
+            need2 = required_bytes(rows2 / k_ring, b2, n2)
             graph_us = None
             if b2 * n2 <= 8192:          # launch-bound shapes: the same launches replayed from a CUDA graph
                 torch.cuda.synchronize()
                 gr = torch.cuda.CUDAGraph()
                 gr.capture_begin()
-                for i in range(32):
-                    q = ptr2[i % k_ring]
-                    fn(h, q[0], q[1], b2, n2, q[2], q[3], ms32, out2.data_ptr(), None, OVERLAP, st)
+                bl2.run(0, 32)
                 gr.capture_end()
                 gr.replay()
                 torch.cuda.synchronize()
+                s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 s0.record(stream)
                 for _ in range(20):
                     gr.replay()
@@ -619,9 +806,76 @@ def run_own(args) -> None:
                 del gr
             other.append({"guesses": b2, "word_slots": n2, "note": tag, "kernel_us": us2,
                           "us_per_step_in_cuda_graph": graph_us,
-                          "guesses_per_s": b2 / (us2 * 1e-6), "achieved_gbs": alg / (us2 * 1e-6) / 1e9,
-                          "frac_of_hbm_peak": alg / (us2 * 1e-6) / 1e9 / peak})
-            del bufs, out2
+                          "guesses_per_s": b2 / (us2 * 1e-6), "live_row_share": rows2 / k_ring / (b2 * n2),
+                          "achieved_gbs": need2 / (us2 * 1e-6) / 1e9,
+                          "frac_of_hbm_peak": need2 / (us2 * 1e-6) / 1e9 / peak,
+                          "frac_survey_formula": survey_bytes(b2, n2) / (us2 * 1e-6) / 1e9 / peak})
+            del bufs, out2, bl2
+
+    # ---- BASELINE configs[3] and [4] on several GPUs: ONE batch sharded over the ranks (strong
+    #      scaling), every rank's slice scored by cm_score_batch_gather so that every rank ends up
+    #      with all the scores; the speed-up is against the same whole batch on one GPU.
+    if world > 1 and gather is not None and not args.no_other_shapes:
+        other = []
+        for (b2, n2, tag) in [(65536, 16, "configs[3]: 65536 guesses x 16 sharded over the ranks, scores all-gathered"),
+                              (16384, 64, "configs[4]: 16384 guesses x 64 sharded over the ranks, scores all-gathered")]:
+            k_ring = 4
+            lo, hi = shard_bounds(b2, world, rank)
+            per = -(-b2 // world)
+            g2 = open_gather(per)
+            if g2 is None:
+                continue
+            full, mine, want_full = [], [], []
+            for i in range(k_ring):            # every rank generates the same whole batches
+                idx2, ln2, _, slot2, ex2 = synth.make_guess_batch(b2, n2, V, N_ANSWERS, seed=7500 + i, near_frac=0.0)
+                want_full.append(eng.score_host(idx2, ln2, slot2, ex2, MIN_SCORE)[0])
+                if rank == 0:
+                    full.append([torch.from_numpy(a).to(dev) for a in (idx2, ln2, slot2, ex2)])
+                mine.append([torch.from_numpy(np.ascontiguousarray(a[lo:hi])).to(dev) for a in (idx2, ln2, slot2, ex2)])
+            out2 = torch.empty(b2, dtype=torch.float32, device=dev)
+            reps = 64
+            one_us = 0.0
+            barrier()
+            if rank == 0:                      # the whole batch on one GPU, the other ranks idle
+                one_us, bl1 = time_shape([tuple(t.data_ptr() for t in q) for q in full], b2, n2, out2.data_ptr(), reps)
+                del bl1, full
+            barrier()
+            one_us = max_over_ranks(one_us)
+            # sharded, gathered
+            ptr_m = [tuple(t.data_ptr() for t in q) for q in mine]
+            bl = BatchList(lib, _lib.cm_batch, eh, g2._h, ptr_m, hi - lo, n2, None, st)
+            bl.run(0, 12)
+            g2.wait(st)
+            barrier()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record(stream)
+            bl.run(0, reps)
+            g2.wait(st)                        # the last step's scores are on every rank when the region ends
+            s1.record(stream)
+            barrier()
+            n_us = max_over_ranks(s0.elapsed_time(s1) * 1e3 / reps)
+            # verification: steps of a short run, the whole gathered batch against a local re-score
+            ok, n_ver = g2.timed_out() == 0, 0
+            for j in range(2 * GATHER_DEPTH + 3):
+                bl.run(j, 1)
+                if j % 2 == 0 or j >= 2 * GATHER_DEPTH - 2:
+                    ptr = g2.wait(st)
+                    got = g2.as_tensor(ptr).cpu().numpy()
+                    for r in range(world):
+                        a, b_ = shard_bounds(b2, world, r)
+                        ok = ok and bool(np.array_equal(got[r, : b_ - a].view(np.uint32),
+                                                        want_full[j % k_ring][a:b_].view(np.uint32)))
+                    n_ver += 1
+            ok = ok and g2.timed_out() == 0
+            t_ok = torch.tensor([1.0 if ok else 0.0], device=dev)
+            dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+            other.append({"guesses": b2, "word_slots": n2, "note": tag, "scaling": "strong",
+                          "guesses_per_rank": per, "us_per_step": n_us, "us_per_step_one_gpu": one_us,
+                          "speedup_vs_one_gpu": one_us / n_us, "guesses_per_s": b2 / (n_us * 1e-6),
+                          "gather_verified": bool(t_ok.item() == 1.0), "gather_verified_steps": n_ver})
+            dist.barrier()
+            g2.close()
+            del mine, out2, bl
 
     # ---- single-call latency on the micro-batch shape (configs[1]: 512 guesses x 8) ------
     lat = None
@@ -702,8 +956,11 @@ def run_own(args) -> None:
                                       + (("scores of every step all-gathered over NVLink peer stores by a ship CTA riding in the next scoring launch (cm_score_batch_gather)"
                                           if gather is not None else "NCCL all_gather of scores")
                                          if world > 1 else "no collective"),
-                       "gather_verified": gather_check, "cpus_near_gpu": near_cpus,
+                       "gather_verified": gather_check, "gather_verified_steps": gather_steps,
+                       "cpus_near_gpu": near_cpus,
+                       "steps_enqueued_by": "cm_score_batch_list_device, one C-ABI call per <= 64 steps",
                        "l2": f"ring of {RING} distinct batches over a 3.6 GB table (inputs >> L2)"},
+            "sustained": sustained,
             "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
             "cpu_baseline": cpu_baseline, "clocks": clocks, "latency": lat, "parity": parity,
             "other_shapes": other, "python_boundary": py_lat,
@@ -717,13 +974,6 @@ def run_own(args) -> None:
         dist.destroy_process_group()
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of cm_score_kernel at 4096x16 from the
-# committed `ncu --set full` capture of the kernel timed above (row loads carry the .L2::64B hint):
-# profiles/r1_v5_4096x16.summary.txt, 75,981,568 B read + 2,135,552 B written.  Algorithmic bytes
-# are 78,938,112: a few rows repeat within a batch and come from L2.  (r1_v4, before the hint: 81,622,272.)
-TRAFFIC_BYTES_PER_LAUNCH = 78_117_120
-
-
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -734,6 +984,7 @@ def main() -> None:
     ap.add_argument("--cpu-budget-s", type=float, default=20.0, help="CPU-seconds of baseline work")
     ap.add_argument("--ref-budget-s", type=float, default=60.0)
     ap.add_argument("--roofline-s", type=float, default=1.0)
+    ap.add_argument("--min-wall-s", type=float, default=0.5, help="length of the `sustained` measurements")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--collective", default="fused", choices=["fused", "nccl"])
     ap.add_argument("--no-other-shapes", action="store_true")

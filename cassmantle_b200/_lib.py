@@ -57,6 +57,7 @@ _SIGNATURES = {
     "cm_pipe_submit": (_c.c_int, [_P, _c.c_int, _c.c_float, _c.c_int]),
     "cm_pipe_wait": (_c.c_int, [_P, _c.c_int]),
     "cm_pipe_cycle": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_float, _c.c_int]),
+    "cm_pipe_cycle_many": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _c.c_int]),
     "cm_vocab_create": (_c.c_int, [_c.POINTER(_P), _P, _P, _P, _c.c_int64]),
     "cm_vocab_destroy": (_c.c_int, [_P]),
     "cm_vocab_size": (_c.c_int, [_P, _c.POINTER(_c.c_int64), _c.POINTER(_c.c_int64)]),
@@ -79,6 +80,7 @@ _SIGNATURES = {
     "cm_gather_stride": (_c.c_int, [_P]),
     "cm_score_batch_gather": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _c.c_int, _P, _P, _c.c_float,
                                          _P, _P, _c.c_uint32, _P]),
+    "cm_score_batch_list_device": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_float, _c.c_uint32, _P]),
     "cm_gather_result": (_c.c_int, [_P, _c.POINTER(_P)]),
     "cm_gather_flush": (_c.c_int, [_P, _P]),
     "cm_gather_wait": (_c.c_int, [_P, _c.POINTER(_P), _P]),
@@ -89,6 +91,12 @@ _SIGNATURES = {
     "cm_score_batch_host": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _P, _P, _c.c_float,
                                        _P, _P]),
 }
+
+class cm_batch(ctypes.Structure):
+    """struct cm_batch of include/cassmantle_b200.h (one entry of cm_score_batch_list_device)."""
+    _fields_ = [("guess_idx", _P), ("guess_len", _P), ("answer_slot", _P), ("exact", _P),
+                ("scores", _P), ("centi", _P), ("n_guesses", _c.c_int32), ("n_slots", _c.c_int32)]
+
 
 _lib = None
 

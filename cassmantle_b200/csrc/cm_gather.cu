@@ -257,6 +257,25 @@ int cm_score_batch_gather(cm_engine *e, cm_gather *g, const int32_t *d_guess_idx
     return CM_OK;
 }
 
+// Several batches in one boundary crossing (a micro-batcher flushing more than one queue, or a
+// producer that has k steps ready): the calls are enqueued back to back, in order, exactly as k
+// separate cm_score_batch_device / cm_score_batch_gather calls would be.
+int cm_score_batch_list_device(cm_engine *e, cm_gather *g, const cm_batch *batches, int n_batches,
+                               float min_score, uint32_t flags, void *stream) {
+    if (n_batches < 0) return fail(CM_ERR_INVALID, "n_batches %d is negative", n_batches);
+    if (n_batches > 0 && batches == nullptr) return fail(CM_ERR_INVALID, "batches is NULL");
+    for (int i = 0; i < n_batches; ++i) {
+        const cm_batch &b = batches[i];
+        const int rc = g != nullptr
+            ? cm_score_batch_gather(e, g, b.guess_idx, b.guess_len, b.n_guesses, b.n_slots, b.answer_slot,
+                                    b.exact, min_score, b.scores, b.centi, flags, stream)
+            : cm_score_batch_device(e, b.guess_idx, b.guess_len, b.n_guesses, b.n_slots, b.answer_slot,
+                                    b.exact, min_score, b.scores, b.centi, flags, stream);
+        if (rc != CM_OK) return rc;
+    }
+    return CM_OK;
+}
+
 int cm_gather_result(cm_gather *g, float **d_gathered) {
     if (g == nullptr || d_gathered == nullptr) return fail(CM_ERR_INVALID, "NULL argument");
     if (g->step == 0) return fail(CM_ERR_STATE, "no gathered launch yet");

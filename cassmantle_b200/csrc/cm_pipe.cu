@@ -214,6 +214,25 @@ int cm_pipe_cycle(cm_pipe *p, int wait_slot, int submit_slot, float min_score, i
     return cm_pipe_submit(p, submit_slot, min_score, want_centi);
 }
 
+// The same for a producer that has `count` batches ready: for i < count, wait for slot
+// (wait_first + i) % depth and submit slot (submit_first + i) % depth, so the number of batches in
+// flight does not change during the call.  Either index may be negative: no waits / no submits.
+int cm_pipe_cycle_many(cm_pipe *p, int wait_first, int submit_first, int count, float min_score,
+                       int want_centi) {
+    if (p == nullptr) return fail(CM_ERR_INVALID, "pipe is NULL");
+    const int depth = (int)p->slots.size();
+    if (count < 0 || count > depth) return fail(CM_ERR_INVALID, "count %d outside [0, %d]", count, depth);
+    if (wait_first >= depth || submit_first >= depth)
+        return fail(CM_ERR_INVALID, "slot index beyond the pipe's %d slots", depth);
+    for (int i = 0; i < count; ++i) {
+        if (wait_first >= 0)
+            if (int rc = cm_pipe_wait(p, (wait_first + i) % depth)) return rc;
+        if (submit_first >= 0)
+            if (int rc = cm_pipe_submit(p, (submit_first + i) % depth, min_score, want_centi)) return rc;
+    }
+    return CM_OK;
+}
+
 int cm_pipe_depth(cm_pipe *p) { return p ? (int)p->slots.size() : 0; }
 
 }  // extern "C"

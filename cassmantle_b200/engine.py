@@ -205,3 +205,10 @@ class ScoringPipe:
         """``wait(wait_slot)`` (skipped when negative) then ``submit(submit_slot)`` in one call."""
         check(self._lib.cm_pipe_cycle(self._h, wait_slot, submit_slot, ctypes.c_float(np.float32(min_score)),
                                       1 if want_centi else 0))
+
+    def cycle_many(self, wait_first: int, submit_first: int, count: int, min_score: float,
+                   want_centi: bool = False) -> None:
+        """``count`` consecutive slots in one call: wait ``wait_first + i``, submit ``submit_first + i``
+        (modulo the depth); a negative index skips the waits / the submits."""
+        check(self._lib.cm_pipe_cycle_many(self._h, wait_first, submit_first, count,
+                                           ctypes.c_float(np.float32(min_score)), 1 if want_centi else 0))

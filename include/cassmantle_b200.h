@@ -155,6 +155,11 @@ int cm_pipe_submit(cm_pipe *p, int slot, float min_score, int want_centi);
 int cm_pipe_wait(cm_pipe *p, int slot);
 /* cm_pipe_wait(wait_slot) (skipped when wait_slot < 0) followed by cm_pipe_submit(submit_slot). */
 int cm_pipe_cycle(cm_pipe *p, int wait_slot, int submit_slot, float min_score, int want_centi);
+/* The same for `count` consecutive slots (modulo the depth) in one call: for i < count,
+ * cm_pipe_wait((wait_first + i) % depth) then cm_pipe_submit((submit_first + i) % depth).
+ * wait_first < 0: no waits; submit_first < 0: no submits.  count <= depth.                  */
+int cm_pipe_cycle_many(cm_pipe *p, int wait_first, int submit_first, int count, float min_score,
+                       int want_centi);
 
 /* ---- vocabulary lookup on the device -------------------------------- *
  * Replaces `inputs.lower()` (src/backend.py:304) + gensim's `key_to_index[word]` dict lookup
@@ -268,6 +273,24 @@ int cm_score_batch_gather(cm_engine *e, cm_gather *g,
                           const int32_t *d_answer_slot, const uint8_t *d_exact,
                           float min_score, float *d_scores, int32_t *d_centi,
                           uint32_t flags, void *stream);
+/* k batches in one call: enqueues cm_score_batch_gather (g != NULL) or cm_score_batch_device
+ * (g == NULL) for batches[0..n_batches) in order on `stream`, with the same min_score and flags,
+ * and stops at the first error.  Device pointers as in those calls (scores may be NULL with a
+ * gather).  The reference scores one request's keys in a loop (src/backend.py:314-316); this is
+ * the batched form of that loop for a caller that has several device batches ready, so that
+ * the host language crosses the boundary once, not k times.                                  */
+typedef struct cm_batch {
+    const int32_t *guess_idx;
+    const int32_t *guess_len;
+    const int32_t *answer_slot;
+    const uint8_t *exact;        /* may be NULL */
+    float *scores;
+    int32_t *centi;              /* may be NULL */
+    int32_t n_guesses;
+    int32_t n_slots;
+} cm_batch;
+int cm_score_batch_list_device(cm_engine *e, cm_gather *g, const cm_batch *batches, int n_batches,
+                               float min_score, uint32_t flags, void *stream);
 int cm_gather_result(cm_gather *g, float **d_gathered);
 int cm_gather_flush(cm_gather *g, void *stream);
 int cm_gather_wait(cm_gather *g, float **d_gathered, void *stream);

@@ -40,9 +40,16 @@ def test_own_arm_line():
     assert d["gpu_launches"] == 60 and d["dtype"] == "f32" and d["scaling"] == "weak" and d["vs_baseline"] is None
     r = d["roofline"]
     assert r["bound"] == "hbm" and r["unit"] == "GB/s" and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
-    assert r["traffic"] and 0.3 < r["frac"] < 1.3
+    assert r["traffic"] and r["traffic_source"] and 0.3 < r["frac"] < 1.3
+    # the fraction is on the bytes the timed batches require (rows of live guesses only); SURVEY's
+    # formula, which charges every guess all its rows, is reported beside it and is larger
+    assert abs(r["achieved"] - r["algorithmic_bytes_per_launch"] / (r["kernel_us"] * 1e-6) / 1e9) < 1e-6 * r["achieved"]
+    assert 0.92 < r["live_row_share"] < 0.96 and r["frac_survey_formula"] > r["frac"]
+    assert r["algorithmic_bytes_per_launch"] < r["survey_formula_bytes_per_launch"]
+    assert d["sustained"]["steps"] >= 60 and d["sustained"]["value"] > 0
     e = d["e2e"]
     assert e["h2d_bytes_per_step"] > 0 and e["d2h_bytes_per_step"] > 0 and e["value"] != d["value"] and e["value"] > 0
+    assert e["sustained"]["steps"] >= 60 and e["one_step_per_call"]["value"] > 0
     cb = d["cpu_baseline"]
     assert {"value", "unit", "cores", "kind", "sample"} <= set(cb) and cb["kind"] == "port"
     assert {"sm_mhz", "sm_max_mhz", "reasons"} <= set(d["clocks"])

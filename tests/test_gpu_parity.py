@@ -144,6 +144,45 @@ def test_device_entry_point_equals_host_entry_point(small_engine):
     assert np.array_equal(out.cpu().numpy().view(np.uint32), want2.view(np.uint32))
 
 
+def test_batch_list_entry_point_equals_single_calls(small_engine):
+    """cm_score_batch_list_device: k batches of different shapes in one C-ABI call."""
+    import ctypes
+    import torch
+    from cassmantle_b200 import _lib
+    lib = _lib.load()
+    dev = torch.device("cuda:0")
+    st = torch.cuda.current_stream().cuda_stream
+    shapes = [(700, 16), (4096, 1), (33, 3), (2048, 8)]
+    keep, wants = [], []
+    arr = (_lib.cm_batch * len(shapes))()
+    ans = None
+    for k, (B, N) in enumerate(shapes):
+        idx, ln, a, slot, ex = synth.make_guess_batch(B, N, 50_000, 2, seed=300 + k, ragged=N > 1)
+        if ans is None:
+            ans = a
+            small_engine.set_answers(ans)
+        wants.append(small_engine.score_host(idx, ln, slot, ex, 0.01, want_centi=True))
+        t = [torch.from_numpy(x).to(dev) for x in (idx, ln, slot, ex)]
+        out = torch.full((B,), -3.0, dtype=torch.float32, device=dev)
+        cen = torch.full((B,), -3, dtype=torch.int32, device=dev)
+        keep.append((t, out, cen))
+        arr[k] = _lib.cm_batch(t[0].data_ptr(), t[1].data_ptr(), t[2].data_ptr(), t[3].data_ptr(),
+                               out.data_ptr(), cen.data_ptr(), B, N)
+    torch.cuda.synchronize()
+    rc = lib.cm_score_batch_list_device(small_engine._h, None, arr, len(shapes), ctypes.c_float(np.float32(0.01)),
+                                        _lib.CM_SCORE_OVERLAP_PREVIOUS, st)
+    assert rc == 0, lib.cm_last_error()
+    torch.cuda.synchronize()
+    for (t, out, cen), (want, want_c) in zip(keep, wants):
+        assert np.array_equal(out.cpu().numpy().view(np.uint32), want.view(np.uint32))
+        assert np.array_equal(cen.cpu().numpy(), want_c)
+    # an error in the middle stops the list and reports which call failed, as that call would
+    arr[1].n_slots = 0
+    assert lib.cm_score_batch_list_device(small_engine._h, None, arr, len(shapes), ctypes.c_float(0.01), 0, st) == -1
+    assert b"n_slots" in lib.cm_last_error()
+    assert lib.cm_score_batch_list_device(small_engine._h, None, None, 0, ctypes.c_float(0.01), 0, st) == 0
+
+
 def test_overlapped_launches_match_serial(small_engine):
     """CM_SCORE_OVERLAP_PREVIOUS: back-to-back independent batches may overlap on the GPU;
     every batch must still come out bit-identical to a serial run, including right after
@@ -365,6 +404,19 @@ def test_pipe_matches_host_entry_point(small_engine, monkeypatch, route):
     assert np.array_equal(pipe.buffers(0, 64, 2)["scores"].view(np.uint32), w0.view(np.uint32))
     pipe.wait(1)
     assert np.array_equal(pipe.buffers(1, 64, 2)["scores"].view(np.uint32), w0.view(np.uint32))
+    # cycle_many: k consecutive slots (modulo the depth) per call
+    for s in (0, 1, 2):
+        v = pipe.buffers(s, 64, 2)
+        v["guess_idx"][:] = idx; v["guess_len"][:] = ln; v["answer_slot"][:] = slot; v["exact"][:] = ex
+        v["scores"][:] = -1.0
+    pipe.cycle_many(-1, 2, 2, 0.01)            # submit slots 2 and 0
+    pipe.cycle_many(2, 1, 1, 0.01)             # wait 2, submit 1
+    assert np.array_equal(pipe.buffers(2, 64, 2)["scores"].view(np.uint32), w0.view(np.uint32))
+    pipe.cycle_many(0, -1, 2, 0.01)            # wait 0 and 1
+    for s in (0, 1):
+        assert np.array_equal(pipe.buffers(s, 64, 2)["scores"].view(np.uint32), w0.view(np.uint32))
+    with pytest.raises(CassMantleError):
+        pipe.cycle_many(0, 1, 4, 0.01)         # more than the pipe has slots
     with pytest.raises(CassMantleError):
         pipe.buffers(0, 4096, 16)              # beyond max_guesses
     with pytest.raises(CassMantleError):
