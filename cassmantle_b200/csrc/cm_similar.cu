@@ -168,7 +168,7 @@ cm_scan_kernel(const float *__restrict__ table, int64_t n_rows, int dim4, const 
     if (sh_hist8[threadIdx.x]) atomicAdd(&ps->hist8[threadIdx.x], sh_hist8[threadIdx.x]);
 }
 
-// The scan laid out like the scoring kernel's gather (rows of 65..80 float4, i.e. 300-d): 16 lanes
+// The scan for 300-d tables, laid out like the scoring kernel's gather (rows of 65..80 float4): 16 lanes
 // x 5 vectors per row, two rows per load instruction, one half-warp walks 16 consecutive rows
 // keeping one partial dot product per row, and a 15-shuffle transpose-reduce at the end leaves
 // row r0 + sub's distance in lane sub.  Many short CTAs (128 rows each, 7 per SM) instead of a
@@ -566,9 +566,11 @@ extern "C" int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_o
         return (unsigned)(c < 0 ? 0 : (c > kBucketCap ? kBucketCap : c));
     }();
     const float *table = e->d_table, *mean = s->d_mean, *norms = s->d_norms;
-    // CM_SCAN16=1 selects the experimental 16-lane scan for 300-d tables (see cm_scan16_kernel)
-    static const bool scan16 = [] { const char *v = getenv("CM_SCAN16"); return v != nullptr && *v == '1'; }();
-    if (scan16 && dim4 > 64 && dim4 <= 80) {
+    // 300-d tables (65..80 float4 per row) take the 16-lane scan: 580 against 594 us per query at
+    // 3M rows, A/B on one box, two runs each (profiles/r2_similar_ab.txt).  Test hook:
+    // CM_SIMILAR_GENERIC_SCAN=1 forces the generic kernel so the two can be compared.
+    static const bool generic_scan = [] { const char *v = getenv("CM_SIMILAR_GENERIC_SCAN"); return v != nullptr && *v == '1'; }();
+    if (!generic_scan && dim4 > 64 && dim4 <= 80) {
         cfg.blockDim = dim3(128);
         cfg.gridDim = dim3((unsigned)((e->n_rows + 127) / 128));
         cudaLaunchKernelEx(&cfg, cm_scan16_kernel<5>, table, e->n_rows, dim4, mean, norms, s->d_dists, s->d_pick);

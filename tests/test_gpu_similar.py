@@ -153,7 +153,7 @@ def _similar_child(env_extra, n_rows, queries):
                 print(q, k, " ".join(map(str, r.tolist())), " ".join(v.hex() for v in s.astype(np.float64)))
     """)
     env = dict(os.environ)
-    env.pop("CM_SCAN16", None)
+    env.pop("CM_SIMILAR_GENERIC_SCAN", None)
     env.update(env_extra)
     return subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, check=True,
                           cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__)))).stdout.splitlines()
@@ -161,7 +161,7 @@ def _similar_child(env_extra, n_rows, queries):
 
 def _compare_scans(n_rows, queries):
     a = _similar_child({}, n_rows, queries)
-    b = _similar_child({"CM_SCAN16": "1"}, n_rows, queries)
+    b = _similar_child({"CM_SIMILAR_GENERIC_SCAN": "1"}, n_rows, queries)
     assert len(a) == len(b) == len(queries)
     for la, lb in zip(a, b):
         fa, fb = la.split(" "), lb.split(" ")
@@ -175,9 +175,9 @@ def _compare_scans(n_rows, queries):
         assert len(set(rows_a) ^ set(rows_b)) <= 4                   # at most a couple of last-ulp swaps at the k-th place
 
 
-def test_opt_in_16_lane_scan_agrees_with_the_default():
+def test_16_lane_scan_agrees_with_the_generic_scan():
     _compare_scans(50_000, [(5, 1), (77, 51), (4242, 1024)])
 
 
-def test_opt_in_16_lane_scan_at_full_size():
+def test_16_lane_scan_agrees_with_the_generic_scan_at_full_size():
     _compare_scans(synth.FULL_ROWS, [(2_718_281, 51), (7, 200)])

@@ -25,10 +25,8 @@ for step in "$@"; do
       CM_FLAGS=1 timeout 600 ncu --set full --clock-control none --import-source on -k regex:cm_score -s 40 -c 1 -f -o $OUT/${TAG}_4096x16 \
           python tools/probe_kernel.py 4096x16 reps=60 > $OUT/${TAG}_ncu_4096x16.log 2>&1; echo "ncu 4096x16 rc=$?" ;;
     similar)
+      CM_SIMILAR_GENERIC_SCAN=1 NO_CPU=1 timeout 300 python tools/bench_similar.py > $OUT/${TAG}_similar_generic.log 2>&1
       NO_CPU=1 timeout 300 python tools/bench_similar.py > $OUT/${TAG}_similar_default.log 2>&1
-      CM_SCAN16=1 NO_CPU=1 timeout 300 python tools/bench_similar.py > $OUT/${TAG}_similar_scan16.log 2>&1
-      NO_CPU=1 timeout 300 python tools/bench_similar.py > $OUT/${TAG}_similar_default2.log 2>&1
-      CM_SCAN16=1 NO_CPU=1 timeout 300 python tools/bench_similar.py > $OUT/${TAG}_similar_scan16b.log 2>&1
       tail -n 3 $OUT/${TAG}_similar_*.log ;;
     probe)
       CM_FLAGS=1 timeout 600 python tools/probe_kernel.py 4096x16 65536x1 4096x1 512x8 65536x16 reps=2000 > $OUT/${TAG}_probe.log 2>&1; tail -n 8 $OUT/${TAG}_probe.log ;;
