@@ -71,6 +71,8 @@ _SIGNATURES = {
     "cm_blur_set_image": (_c.c_int, [_P, _P, _c.c_int, _c.c_int]),
     "cm_blur_batch_host": (_c.c_int, [_P, _P, _c.c_int, _P]),
     "cm_blur_batch_pinned": (_c.c_int, [_P, _P, _c.c_int, _c.POINTER(_P)]),
+    "cm_blur_batch_jpeg": (_c.c_int, [_P, _P, _c.c_int, _c.c_int, _P, _c.c_int64, _P]),
+    "cm_blur_batch_jpeg_pinned": (_c.c_int, [_P, _P, _c.c_int, _c.c_int, _c.POINTER(_P), _c.POINTER(_P)]),
     "cm_gather_create": (_c.c_int, [_c.POINTER(_P), _P, _c.c_int, _c.c_int, _c.c_int, _c.c_int]),
     "cm_gather_destroy": (_c.c_int, [_P]),
     "cm_gather_export": (_c.c_int, [_P, _P]),

@@ -83,6 +83,30 @@ class ImageBlur:
         """Batched ``mask_image``: one blurred copy of the current image per session score."""
         return self.blur_radii([self.score_to_blur(float(s)) for s in scores], copy=copy)
 
+    def blur_radii_jpeg(self, radii: Sequence[float], quality: int = 75) -> list:
+        """The current image under GaussianBlur(radius), saved as JPEG, for each radius: a list of
+        ``bytes`` equal to what ``image.filter(GaussianBlur(r)).save(buf, 'JPEG', quality=quality)``
+        writes (main.py:100-103 uses Pillow's default quality, 75).  RGB images only."""
+        if self.shape is None:
+            raise RuntimeError("set_image() first")
+        r = np.ascontiguousarray(radii, dtype=np.float32)
+        files = []
+        for lo in range(0, r.size, self.max_batch):
+            part = r[lo:lo + self.max_batch]
+            p, q = ctypes.c_void_p(), ctypes.c_void_p()
+            check(self._lib.cm_blur_batch_jpeg_pinned(self._h, part.ctypes.data, part.size, int(quality),
+                                                      ctypes.byref(p), ctypes.byref(q)))
+            off = np.ctypeslib.as_array(ctypes.cast(q, ctypes.POINTER(ctypes.c_int64)), shape=(part.size + 1,))
+            block = ctypes.cast(p, ctypes.POINTER(ctypes.c_uint8))
+            files += [ctypes.string_at(ctypes.addressof(block.contents) + int(off[i]), int(off[i + 1] - off[i]))
+                      for i in range(part.size)]
+        return files
+
+    def mask_images_jpeg(self, scores: Sequence[float], quality: int = 75) -> list:
+        """Batched ``mask_image`` + ``image.save(img_io, 'JPEG')`` (src/server.py:129-133, main.py:100-103):
+        the JPEG file of the blurred image for each session score."""
+        return self.blur_radii_jpeg([self.score_to_blur(float(s)) for s in scores], quality=quality)
+
     def mask_image(self, image, score: float):
         """Same call as src/backend.py:322-324 (uploads ``image``; prefer set_image + mask_images)."""
         from PIL import Image

@@ -31,20 +31,7 @@
 
 #include "cm_internal.h"
 
-struct cm_blur {
-    int device = 0;
-    int max_h = 0, max_w = 0, channels = 0, max_batch = 0;
-    int h = 0, w = 0;                 // current image
-    uint8_t *d_src = nullptr;         // the round's image
-    uint8_t *d_a = nullptr;           // ping  [max_batch][h*w*c]
-    uint8_t *d_b = nullptr;           // pong
-    uint8_t *h_pin = nullptr;         // pinned staging for results
-    void *d_params = nullptr;         // BoxParams[max_batch]
-    cudaStream_t stream = nullptr;
-    cudaStream_t copy_stream = nullptr;   // results of chunk i travel while chunk i+1 is blurred
-    cudaEvent_t blurred[2] = {nullptr, nullptr};
-    std::mutex mu;
-};
+#include "cm_blur_state.h"
 
 namespace {
 
@@ -258,6 +245,7 @@ int cm_blur_destroy(cm_blur *b) {
         if (b->d_b) cudaFree(b->d_b);
         if (b->d_params) cudaFree(b->d_params);
         if (b->h_pin) cudaFreeHost(b->h_pin);
+        cm::jpeg_state_free(b);
     }
     delete b;
     return CM_OK;
@@ -312,8 +300,8 @@ int cm_blur_set_image(cm_blur *b, const uint8_t *pixels, int height, int width) 
     return CM_OK;
 }
 
-// Blurs into the device ping-pong buffers and brings the n images back into b->h_pin (b->mu held).
-static int blur_batch_to_pinned(cm_blur *b, const float *radii, int n, size_t *bytes_out) {
+// Validates the radii and uploads the per-request box parameters (b->mu held, device current).
+static int upload_params(cm_blur *b, const float *radii, int n) {
     if (b->h == 0) return fail(CM_ERR_STATE, "cm_blur_set_image has not been called");
     std::vector<BoxParams> params((size_t)n);
     for (int i = 0; i < n; ++i) {
@@ -323,8 +311,32 @@ static int blur_batch_to_pinned(cm_blur *b, const float *radii, int n, size_t *b
             return fail(CM_ERR_INVALID, "radius %g of request %d outside [-4096, 4096]", (double)radii[i], i);
         params[(size_t)i] = box_params(radii[i]);
     }
-    cm::DeviceGuard guard(b->device);
+    // pageable source: the runtime stages it before returning, so `params` may go out of scope
     CM_CUDA(cudaMemcpyAsync(b->d_params, params.data(), sizeof(BoxParams) * n, cudaMemcpyHostToDevice, b->stream));
+    return CM_OK;
+}
+
+static int blur_chunk(cm_blur *b, int first, int count) {
+    switch (b->channels) {
+        case 1: return blur_batch<1>(b, first, count);
+        case 3: return blur_batch<3>(b, first, count);
+        default: return blur_batch<4>(b, first, count);
+    }
+}
+
+}  // extern "C"
+
+int cm::blur_enqueue(cm_blur *b, const float *radii, int n) {
+    if (int rc = upload_params(b, radii, n)) return rc;
+    return blur_chunk(b, 0, n);
+}
+
+extern "C" {
+
+// Blurs into the device ping-pong buffers and brings the n images back into b->h_pin (b->mu held).
+static int blur_batch_to_pinned(cm_blur *b, const float *radii, int n, size_t *bytes_out) {
+    cm::DeviceGuard guard(b->device);
+    if (int rc = upload_params(b, radii, n)) return rc;
     // In chunks of about 16 MB of pixels: while one chunk is being blurred the previous one is
     // already on its way to the host (1024x1024 RGB: the copy is the longer of the two).
     const size_t img = (size_t)b->h * b->w * b->channels;
@@ -332,13 +344,7 @@ static int blur_batch_to_pinned(cm_blur *b, const float *radii, int n, size_t *b
     int k = 0;
     for (int first = 0; first < n; first += chunk, ++k) {
         const int count = std::min(chunk, n - first);
-        int rc;
-        switch (b->channels) {
-            case 1: rc = blur_batch<1>(b, first, count); break;
-            case 3: rc = blur_batch<3>(b, first, count); break;
-            default: rc = blur_batch<4>(b, first, count); break;
-        }
-        if (rc != CM_OK) return rc;
+        if (int rc = blur_chunk(b, first, count)) return rc;
         CM_CUDA(cudaEventRecord(b->blurred[k & 1], b->stream));
         CM_CUDA(cudaStreamWaitEvent(b->copy_stream, b->blurred[k & 1], 0));
         CM_CUDA(cudaMemcpyAsync(b->h_pin + (size_t)first * img, b->d_b + (size_t)first * img, (size_t)count * img,

@@ -231,6 +231,24 @@ int cm_blur_batch_host(cm_blur *b, const float *radii, int n, uint8_t *out);
  * the pixels right away -- src/server.py:131-133 saves them as JPEG -- needs no more).      */
 int cm_blur_batch_pinned(cm_blur *b, const float *radii, int n, const uint8_t **out);
 
+/* The blurred images as JPEG FILES, which is what the reference sends: GET /fetch/contents saves
+ * the blurred PIL image with Pillow's defaults, main.py:100-103 `image.save(img_io, 'JPEG')` (the
+ * same call in src/utils.py:12-16 encode_image), and base64-encodes the bytes (main.py:106).
+ * Blur (as above) and libjpeg's baseline encoder restated on the device -- RGB->YCbCr, 4:2:0
+ * down-sampling, integer 8x8 DCT, quantisation, standard Huffman tables, JFIF header -- so file i
+ * equals, byte for byte, what Pillow writes for request i.  RGB objects only (channels == 3;
+ * Pillow refuses RGBA as JPEG, the reference's image is RGB).  quality: 1..100 as in Pillow's
+ * `quality=`, 0 = Pillow's default 75 (what the reference uses).  File i is
+ * out[offsets[i] .. offsets[i + 1]); offsets has n + 1 entries.  Blocking.
+ * cm_blur_batch_jpeg copies into the caller's buffer and returns CM_ERR_NOMEM, with offsets[]
+ * filled in (offsets[n] = bytes needed), when `capacity` is too small or out is NULL;
+ * cm_blur_batch_jpeg_pinned returns pointers into the object's own page-locked block, valid
+ * until the next call on `b`.  ~10x fewer bytes cross PCIe than with cm_blur_batch_host.      */
+int cm_blur_batch_jpeg(cm_blur *b, const float *radii, int n, int quality, uint8_t *out,
+                       int64_t capacity, int64_t *offsets);
+int cm_blur_batch_jpeg_pinned(cm_blur *b, const float *radii, int n, int quality,
+                              const uint8_t **out, const int64_t **offsets);
+
 /* ---- several GPUs: score all-gather over NVLink peer memory ---------------------------- *
  * No reference counterpart (the reference has no collective).  SURVEY.md §8e: one process
  * per GPU, a table replica each, every rank scores its slice of the batch and every rank
