@@ -9,6 +9,7 @@
 #include "cm_ship.cuh"
 
 struct cm_similar_state;   // scratch of cm_most_similar (cm_similar.cu), allocated on first use
+struct cm_resident;        // the resident micro-batch kernel's mailbox and state (cm_scorer.cu)
 
 struct cm_engine {
     int device = 0;
@@ -23,6 +24,9 @@ struct cm_engine {
     unsigned char *h_stage = nullptr;
     size_t stage_bytes = 0;
     cm_similar_state *similar = nullptr;
+    cm_resident *resident = nullptr;         // non-NULL once cm_engine_arm_resident has been called
+    cudaEvent_t answers_done = nullptr;      // recorded after cm_set_answers launches while `resident` exists
+    bool answers_pending = false;            // the resident path must wait for answers_done once
     std::mutex mu;
 };
 
@@ -62,6 +66,8 @@ int check_engine(const cm_engine *e);
 void similar_state_free(cm_engine *e);     // cm_similar.cu
 int ensure_stage(cm_engine *e, size_t bytes);   // e->h_stage holds at least `bytes` (call with e->mu held)
 void similar_invalidate(cm_engine *e);     // the table changed: cached row norms are stale
+void resident_stop(cm_engine *e);          // stop the resident kernel if it runs (it is re-launched on demand)
+void resident_free(cm_engine *e);
 
 // Validates the arguments and enqueues the scoring kernel; pointers may be device memory or
 // pinned host memory (the kernel then reads / writes it across PCIe itself).  `ship`, if not

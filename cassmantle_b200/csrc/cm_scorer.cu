@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -169,16 +170,19 @@ cm_answer_unit_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
 //   phase 2  / N, unitvec through an fp64 norm, fp32 dot with the answer's unit vector,
 //            floor at min_score, optional hundredths of a percent
 // --------------------------------------------------------------------------------------
-template <int VPL, int LPG, int R, bool STREAM, int THREADS, bool SINGLE>
+// SYS = true is the resident kernel (below): the batch is a block of per-guess records that the CTA
+// has staged in shared memory, and the answers -- rewritten by cm_set_answers while the kernel is
+// resident -- are read with L2-only loads, issued before the gather (a micro-batch is a latency
+// chain, not bandwidth).  SYS = false: the launched kernels, packed arrays.
+template <int VPL, int LPG, int R, bool STREAM, int THREADS, bool SINGLE, bool SYS = false>
 __device__ __forceinline__ void
-score_groups(const float *__restrict__ table, int64_t n_rows, int dim4,
+score_groups(int warp, const float *__restrict__ table, int64_t n_rows, int dim4,
              const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
              int n_guesses, int n_slots,
              const float *__restrict__ ans_unit, const int32_t *__restrict__ ans_rows,
              int n_answers, const int32_t *__restrict__ answer_slot,
              const uint8_t *__restrict__ exact, float min_score,
-             float *__restrict__ scores, int32_t *__restrict__ centi, uint32_t flags,
-             int first_cta) {
+             float *__restrict__ scores, int32_t *__restrict__ centi, uint32_t flags, int rec_stride = 0) {
     constexpr int G = 32 / LPG;
     // Programmatic dependent launch: let the next launch on the stream start scheduling now,
     // and unless the caller vouched for the inputs (CM_SCORE_OVERLAP_PREVIOUS) wait for the
@@ -189,17 +193,27 @@ score_groups(const float *__restrict__ table, int64_t n_rows, int dim4,
     const int lane = threadIdx.x & 31;
     const int sub = lane & (LPG - 1);
     const int grp_base = lane & ~(LPG - 1);
-    const int warp = ((int)blockIdx.x - first_cta) * (THREADS / 32) + (threadIdx.x >> 5);
     const int b_raw = warp * G + lane / LPG;
     if (warp * G >= n_guesses) return;                      // whole warp out of range
     const bool have = b_raw < n_guesses;
     const int b = have ? b_raw : n_guesses - 1;             // keep every lane's loads in bounds
 
     // ---- phase 0: independent loads, one DRAM round trip ---------------------------------
-    const int32_t *gi = guess_idx + (size_t)b * n_slots;
-    const bool is_exact = (exact != nullptr) && (exact[b] != 0);
-    int n = guess_len[b];
-    const int slot = answer_slot[b];
+    // SYS: guess b is one record of rec_stride ints, {len, slot, exact, index 0, index 1, ...}, which
+    // guess_len points at (guess_idx points at its fourth int); shared memory, broadcast reads.
+    const int32_t *gi = guess_idx + (size_t)b * (SYS ? rec_stride : n_slots);
+    bool is_exact;
+    int n, slot;
+    if constexpr (SYS) {
+        const int32_t *rec = guess_len + (size_t)b * rec_stride;
+        n = rec[0];
+        slot = rec[1];
+        is_exact = rec[2] != 0;
+    } else {
+        is_exact = (exact != nullptr) && (exact[b] != 0);
+        n = guess_len[b];
+        slot = answer_slot[b];
+    }
     // SINGLE (n_slots == 1, the reference's own shape): every lane of the group reads the one index
     int32_t mine = SINGLE ? gi[0] : ((sub < n_slots) ? gi[sub] : -1);
     n = n < 0 ? 0 : (n > n_slots ? n_slots : n);
@@ -223,6 +237,18 @@ score_groups(const float *__restrict__ table, int64_t n_rows, int dim4,
     const int n_live = active ? n : 0;
     const int n_max = (G == 1) ? n_live : __reduce_max_sync(cm::kFullMask, n_live);
 
+    // SYS: the answer's row and unit vector depend only on the slot -- ask for them before the gather
+    int32_t ar_pre = -1;
+    float4 w_pre[SYS ? VPL : 1];
+    if constexpr (SYS) {
+        ar_pre = slot_ok ? __ldcg(ans_rows + slot) : -1;
+        const float4 *u = reinterpret_cast<const float4 *>(ans_unit) + (size_t)(slot_ok ? slot : 0) * dim4;
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+            const int j = sub + LPG * v;
+            w_pre[v] = j < dim4 ? __ldcg(u + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
     float4 acc[VPL];
 #pragma unroll
     for (int v = 0; v < VPL; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -272,7 +298,7 @@ score_groups(const float *__restrict__ table, int64_t n_rows, int dim4,
     // launch shares with its predecessor: from here on the previous kernel must be complete.
     if (overlap) cm::pdl_wait();
     {
-        const int32_t ar = slot_ok ? ans_rows[slot] : -1;     // unknown answer = KeyError too
+        const int32_t ar = SYS ? ar_pre : (slot_ok ? ans_rows[slot] : -1);     // unknown answer = KeyError too
         bad = bad || ar < 0 || (int64_t)ar >= n_rows;
     }
     if (!SINGLE && n_max > 1) {                              // warp-uniform; x / 1 is exact anyway
@@ -293,7 +319,7 @@ score_groups(const float *__restrict__ table, int64_t n_rows, int dim4,
         for (int v = 0; v < VPL; ++v) {
             const int j = sub + LPG * v;
             if (j < dim4) {
-                const float4 w = u[j];       // plain load: written by the answer kernel, maybe just now
+                const float4 w = SYS ? w_pre[SYS ? v : 0] : u[j];   // not .nc: written by the answer kernel, maybe just now
                 p = fmaf(acc[v].x, w.x, p);
                 p = fmaf(acc[v].y, w.y, p);
                 p = fmaf(acc[v].z, w.z, p);
@@ -331,8 +357,9 @@ cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
         return;
     }
     score_groups<VPL, LPG, R, STREAM, THREADS, SINGLE>(
+        ((int)blockIdx.x - n_ship_ctas) * (THREADS / 32) + (int)(threadIdx.x >> 5),
         table, n_rows, dim4, guess_idx, guess_len, n_guesses, n_slots, ans_unit, ans_rows, n_answers,
-        answer_slot, exact, min_score, scores, centi, flags, n_ship_ctas);
+        answer_slot, exact, min_score, scores, centi, flags);
 }
 
 // --------------------------------------------------------------------------------------
@@ -433,6 +460,151 @@ cm_score1_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
         w = w_next;
     }
     if (!waited) cm::pdl_wait();
+}
+
+
+// --------------------------------------------------------------------------------------
+// Resident kernel for micro-batches (cm_engine_arm_resident).  One blocking host call for a few
+// hundred guesses is dominated by the launch and the stream synchronisation around a 4 us
+// kernel (configs[1]).  Armed, the engine keeps this kernel resident -- one CTA per SM, spinning at
+// low duty -- and a call costs two PCIe crossings and no launch:
+//   host   packs the batch into the page-locked mailbox, one record per guess, pre-fills the results
+//          with a sentinel, then stores the 64-bit doorbell (sequence number, batch shape)
+//   CTA 0  polls doorbell + parameters (one 16-byte read across PCIe) and republishes them in device memory
+//   all    spin on that device word; each CTA fetches the records of ITS consecutive guesses once, into
+//          shared memory, scores them with the same code as the launched kernels (score_groups) and
+//          writes the results back into the mailbox; the host watches the sentinels disappear (plain
+//          posted stores, no fence: the host touches nothing of a request before all its results landed)
+// Measured on B200: when several warps read the SAME 32-byte sector of host memory the reads are
+// served one PCIe round trip (0.8 us) after the other -- 592 warps reading one parameter word took
+// 470 us.  Hence one reader for the header, a batch layout of one record per guess in sectors of its
+// own (resident_rec_stride) instead of the packed arrays of the launch path, and every sector asked
+// for exactly once.
+// The kernel leaves by itself after `idle_ns` without a doorbell (so a device-wide synchronisation
+// elsewhere in the process -- cudaFree, cudaDeviceSynchronize -- never waits longer than that) and on
+// a stop doorbell; the host re-launches it on demand.
+// --------------------------------------------------------------------------------------
+struct ResidentMailbox {                 // page-locked host memory; the first 16 bytes are read in one load
+    unsigned long long doorbell;         // seq << 32 | (n_slots - 1) << 20 | (n_guesses - 1) << 8 | stop << 1 | centi
+    unsigned long long params;           // n_answers << 32 | bits of min_score
+    unsigned alive;                      // written 0 by the kernel when it leaves
+    unsigned pad[11];
+};
+constexpr unsigned long long kDoorStop = 2ull, kDoorIdle = 4ull;      // the host never sets kDoorIdle
+constexpr int kResidentThreads = 128, kResidentCtas = 148;
+// Measured on B200 (tools/probe_resident.py, blocking call p50, launch path / resident): 2x1 16.3 / 9.9 us,
+// 64x1 18.2 / 11.2, 512x8 26.6 / 19.6, 1024x1 19.1 / 16.6, 1024x4 24.4 / 23.1, 2048x1 20.8 / 22.2,
+// 2048x8 34.0 / 50.1 -- beyond ~1000 guesses or ~4000 rows the PCIe reads of the records and the four
+// warps per SM cost more than the launch they save.
+constexpr int kResidentMaxGuesses = 1024, kResidentMaxRows = 4096;
+constexpr int kRecHeaderInts = 3;        // record: len, slot, exact, then the indices
+// a CTA stages ceil(B / 148) records: at most 7 x 8 ints (1024 x 4) or 1 x 4104 (1 x 4096)
+constexpr int kResidentSmemInts = 4224;
+
+// ints per record, rounded up to whole 32-byte sectors
+__host__ __device__ inline int resident_rec_stride(int n_slots) { return (kRecHeaderInts + n_slots + 7) & ~7; }
+
+struct ResidentArgs {
+    const float *table;
+    int64_t n_rows;
+    int dim4;
+    const float *ans_unit;
+    const int32_t *ans_rows;
+    ResidentMailbox *box;                // host
+    const int32_t *records;              // host: the batch, one record per guess
+    float *scores;                       // host: the results
+    int32_t *centi;
+    unsigned long long *flag;            // device: [0] the doorbell as CTA 0 last saw it, [1] its params
+    unsigned long long last;             // doorbell value the host considers done
+    unsigned long long idle_ns;
+    unsigned long long *trace;           // developer aid (CM_RESIDENT_TRACE=1): device timestamps in the mailbox, or NULL
+};
+
+template <int VPL>
+__global__ void __launch_bounds__(kResidentThreads)
+cm_resident_kernel(const ResidentArgs a) {
+    __shared__ unsigned long long s_door, s_params;
+    __shared__ int32_t s_rec[kResidentSmemInts];
+    unsigned long long last = a.last;
+    for (;;) {
+        if (threadIdx.x == 0) {
+            unsigned long long d, prm = 0;
+            if (blockIdx.x == 0) {
+                // the ONLY reader of the mailbox header: doorbell and params in one 16-byte PCIe read
+                const unsigned long long t0 = cm::global_ns();
+                for (;;) {
+                    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(d), "=l"(prm) : "l"(&a.box->doorbell) : "memory");
+                    if (d != last) break;
+                    if (cm::global_ns() - t0 > a.idle_ns) { d = last | kDoorStop | kDoorIdle; break; }    // idle: leave
+                }
+                // No system-scope fence here (measured: +1.5 us per request).  The records are read only
+                // after this value has travelled through the device flag to the other CTAs, by PCIe reads
+                // issued later than the one that returned it, and the host wrote them before the doorbell.
+                a.flag[1] = prm;
+                asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(a.flag), "l"(d) : "memory");
+            } else {
+                for (;;) {
+                    asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(d) : "l"(a.flag) : "memory");
+                    if (d != last) break;
+                    __nanosleep(64);
+                }
+                prm = __ldcg(a.flag + 1);
+            }
+            s_door = d;
+            s_params = prm;
+        }
+        __syncthreads();
+        const unsigned long long door = s_door, params = s_params;
+        __syncthreads();
+        if (a.trace != nullptr && threadIdx.x == 0 && blockIdx.x < 2) a.trace[blockIdx.x] = cm::global_ns();   // 0: doorbell seen, 1: flag seen
+        if (door & kDoorStop) break;
+        last = door;
+        const int n_guesses = (int)((door >> 8) & 0xfffu) + 1;
+        const int n_slots = (int)((door >> 20) & 0xfffu) + 1;
+        const float min_score = __uint_as_float((unsigned)params);
+        const int n_answers = (int)(params >> 32);
+        int32_t *centi = (door & 1ull) ? a.centi : nullptr;
+        // This CTA's share: `per` consecutive guesses.  Their records are contiguous in the mailbox and are
+        // fetched once, by the whole CTA, with coalesced volatile loads (never served from a cache line of
+        // an earlier batch; every 32-byte sector asked for exactly once) into shared memory.
+        const int rec = resident_rec_stride(n_slots);
+        const int per = (n_guesses + (int)gridDim.x - 1) / (int)gridDim.x;
+        const int g0 = (int)blockIdx.x * per;
+        const int cnt = min(per, n_guesses - g0);
+        if (cnt > 0) {
+            const int32_t *src = a.records + (size_t)g0 * rec;
+            for (int i = threadIdx.x; i < cnt * rec; i += kResidentThreads)
+                asm volatile("ld.volatile.global.s32 %0, [%1];" : "=r"(s_rec[i]) : "l"(src + i) : "memory");
+        }
+        __syncthreads();
+        if (a.trace != nullptr && threadIdx.x == 0 && blockIdx.x == 1) a.trace[3] = cm::global_ns();           // 3: records staged
+        if (cnt > 0) {
+            const int lw = (int)(threadIdx.x >> 5);
+            float *scores = a.scores + g0;
+            int32_t *cen = centi != nullptr ? centi + g0 : nullptr;
+            bool done = false;
+            if constexpr (VPL == 3) {    // 300-d tables, one word per guess: the 8-lane kernel's arithmetic
+                if (n_slots == 1 && a.dim4 == 75) {
+                    for (int w = lw; w * 4 < cnt; w += kResidentThreads / 32)
+                        score_groups<10, 8, 1, true, kResidentThreads, true, true>(
+                            w, a.table, a.n_rows, a.dim4, s_rec + kRecHeaderInts, s_rec, cnt, 1, a.ans_unit, a.ans_rows,
+                            n_answers, nullptr, nullptr, min_score, scores, cen, 0u, rec);
+                    done = true;
+                }
+            }
+            if (!done) {
+                // R = 8 rows per round where registers allow: a resident micro-batch is latency, not bytes in flight
+                for (int w = lw; w < cnt; w += kResidentThreads / 32)
+                    score_groups<VPL, 32, (VPL <= 3 ? 8 : 2), true, kResidentThreads, false, true>(
+                        w, a.table, a.n_rows, a.dim4, s_rec + kRecHeaderInts, s_rec, cnt, n_slots, a.ans_unit, a.ans_rows,
+                        n_answers, nullptr, nullptr, min_score, scores, cen, 0u, rec);
+            }
+        }
+        if (a.trace != nullptr && threadIdx.x == 0 && blockIdx.x == 1) a.trace[2] = cm::global_ns();           // 2: scored
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(&a.box->alive), "r"(0u) : "memory");
+    }
 }
 
 }  // namespace
