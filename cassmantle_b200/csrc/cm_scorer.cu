@@ -851,6 +851,7 @@ int cm_engine_create(cm_engine **out, int device, int64_t n_rows, int dim) {
     if (err == cudaSuccess) err = cudaMalloc(&e->d_ans_unit, (size_t)CM_MAX_ANSWERS * dim * sizeof(float));
     if (err == cudaSuccess) err = cudaMalloc(&e->d_ans_rows, (size_t)CM_MAX_ANSWERS * sizeof(int32_t));
     if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking);
+    if (err == cudaSuccess) err = cudaEventCreateWithFlags(&e->answers_done, cudaEventDisableTiming);
     if (err != cudaSuccess) {
         cudaGetLastError();
         const int code = fail(err == cudaErrorMemoryAllocation ? CM_ERR_NOMEM : CM_ERR_CUDA,
@@ -867,7 +868,9 @@ int cm_engine_destroy(cm_engine *e) {
     if (e == nullptr) return CM_OK;
     {
         DeviceGuard guard(e->device);
+        cm::resident_free(e);
         if (e->stream) { cudaStreamSynchronize(e->stream); cudaStreamDestroy(e->stream); }
+        if (e->answers_done) cudaEventDestroy(e->answers_done);
         cm::similar_state_free(e);
         if (e->d_table) cudaFree(e->d_table);
         if (e->d_ans_unit) cudaFree(e->d_ans_unit);
@@ -885,6 +888,7 @@ int cm_engine_upload_rows(cm_engine *e, const float *rows, int64_t row0, int64_t
         return fail(CM_ERR_INVALID, "rows [%lld, %lld) outside the %lld-row table",
                     (long long)row0, (long long)(row0 + n), (long long)e->n_rows);
     DeviceGuard guard(e->device);
+    cm::resident_stop(e);                    // it reads the table through the non-coherent path
     const size_t bytes = (size_t)n * e->dim * sizeof(float);
     unsigned char *dst = reinterpret_cast<unsigned char *>(e->d_table + (size_t)row0 * e->dim);
     const unsigned char *src = reinterpret_cast<const unsigned char *>(rows);
@@ -947,6 +951,7 @@ int cm_engine_fill_synthetic(cm_engine *e, uint32_t seed) {
     if ((uint64_t)e->n_rows * (uint64_t)e->dim > 0xffffffffull)
         return fail(CM_ERR_INVALID, "synthetic fill needs n_rows*dim < 2^32");
     DeviceGuard guard(e->device);
+    cm::resident_stop(e);
     cm_synth_fill_kernel<<<148 * 8, 256, 0, e->stream>>>(e->d_table, e->n_rows, e->dim, seed);
     cm::count_launch();
     CM_CUDA(cudaGetLastError());
@@ -991,6 +996,10 @@ int cm_set_answers_device(cm_engine *e, const int32_t *d_answer_rows, int n_answ
     CM_DISPATCH_VPL(e->dim, CM_CALL)
 #undef CM_CALL
     CM_CUDA(cudaGetLastError());
+    if (e->resident != nullptr) {            // the resident kernel is not ordered behind `st` by the stream
+        CM_CUDA(cudaEventRecord(e->answers_done, st));
+        e->answers_pending = true;
+    }
     return CM_OK;
 }
 
@@ -1015,6 +1024,221 @@ int cm_score_batch_device(cm_engine *e, const int32_t *d_guess_idx, const int32_
                              min_score, d_scores, d_centi, flags, (cudaStream_t)stream);
 }
 
+}  // extern "C"
+
+// ---- resident micro-batch kernel: host side ---------------------------------------------------
+struct cm_resident {
+    unsigned char *h_block = nullptr;        // page-locked: mailbox header, records, results
+    ResidentMailbox *box = nullptr;
+    int32_t *records = nullptr, *centi = nullptr;
+    float *scores = nullptr;
+    unsigned long long *h_last = nullptr;    // page-locked source of the flag reset
+    unsigned long long *d_flag = nullptr;
+    cudaStream_t stream = nullptr;
+    unsigned long long last = 0;             // doorbell value of the last completed request
+    uint32_t seq = 0;
+    unsigned long long idle_ns = 0;
+    bool armed = false;
+    double host_trace[3] = {0, 0, 0};        // us: entry -> doorbell, doorbell -> first result, doorbell -> all results
+};
+
+namespace {
+
+int resident_launch(cm_engine *e) {
+    cm_resident *r = e->resident;
+    ResidentArgs a;
+    a.table = e->d_table; a.n_rows = e->n_rows; a.dim4 = e->dim / 4;
+    a.ans_unit = e->d_ans_unit; a.ans_rows = e->d_ans_rows;
+    a.box = r->box; a.records = r->records;
+    a.scores = r->scores; a.centi = r->centi; a.flag = r->d_flag;
+    a.last = r->last; a.idle_ns = r->idle_ns;
+    a.trace = getenv("CM_RESIDENT_TRACE") != nullptr ? reinterpret_cast<unsigned long long *>(r->h_block + 192) : nullptr;
+    *r->h_last = r->last;                    // workers compare the device flag with `last`: start them equal
+    CM_CUDA(cudaMemcpyAsync(r->d_flag, r->h_last, sizeof(unsigned long long), cudaMemcpyHostToDevice, r->stream));
+    r->box->alive = 1u;
+    std::atomic_thread_fence(std::memory_order_seq_cst);
+#define CM_CALL(V) cm_resident_kernel<V><<<kResidentCtas, kResidentThreads, 0, r->stream>>>(a)
+    CM_DISPATCH_VPL(e->dim, CM_CALL)
+#undef CM_CALL
+    cm::count_launch();
+    CM_CUDA(cudaGetLastError());
+    return CM_OK;
+}
+
+inline bool resident_alive(const cm_resident *r) {
+    return *reinterpret_cast<const volatile unsigned *>(&r->box->alive) != 0u;
+}
+
+inline void ring(cm_resident *r, unsigned long long door) {
+    std::atomic_thread_fence(std::memory_order_release);
+    *reinterpret_cast<volatile unsigned long long *>(&r->box->doorbell) = door;
+}
+
+// One micro-batch through the resident kernel (e->mu held, device current).
+int resident_score(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_len, int n_guesses,
+                   int n_slots, const int32_t *answer_slot, const uint8_t *exact, float min_score,
+                   float *scores, int32_t *centi) {
+    cm_resident *r = e->resident;
+    const auto t_enter = std::chrono::steady_clock::now();
+    const size_t B = (size_t)n_guesses, N = (size_t)n_slots;
+    if (e->answers_pending) {                // cm_set_answers ran on some stream: its unit vectors must be complete
+        CM_CUDA(cudaEventSynchronize(e->answers_done));
+        e->answers_pending = false;
+    }
+    {   // one record per guess: {len, slot, exact, indices...}, whole 32-byte sectors
+        const int rec = resident_rec_stride(n_slots);
+        int32_t *out = r->records;
+        const int32_t *src = guess_idx;
+        for (size_t b = 0; b < B; ++b, out += rec, src += N) {
+            out[0] = guess_len[b];
+            out[1] = answer_slot[b];
+            out[2] = exact ? (int32_t)exact[b] : 0;
+            if (N <= 16) {                   // a call to memcpy per guess costs more than the copy
+                for (size_t k = 0; k < N; ++k) out[kRecHeaderInts + k] = src[k];
+            } else {
+                memcpy(out + kRecHeaderInts, src, N * 4);
+            }
+        }
+    }
+    memset(r->scores, 0xff, B * 4);          // sentinel: a NaN no result can be, and not a valid hundredths value
+    if (centi) memset(r->centi, 0xff, B * 4);
+    uint32_t ms_bits;
+    memcpy(&ms_bits, &min_score, 4);
+    *reinterpret_cast<volatile unsigned long long *>(&r->box->params) =
+        ((unsigned long long)(uint32_t)e->n_answers << 32) | ms_bits;
+    if (!resident_alive(r))
+        if (int rc = resident_launch(e)) return rc;
+    const unsigned long long door = ((unsigned long long)(++r->seq) << 32) | ((unsigned long long)(N - 1) << 20) |
+                                    ((unsigned long long)(B - 1) << 8) | (centi ? 1ull : 0ull);
+    const auto t_ring = std::chrono::steady_clock::now();
+    r->host_trace[0] = std::chrono::duration<double, std::micro>(t_ring - t_enter).count();
+    ring(r, door);
+    bool first_seen = false;
+    const volatile uint32_t *ws = reinterpret_cast<const volatile uint32_t *>(r->scores);
+    const volatile uint32_t *wc = centi ? reinterpret_cast<const volatile uint32_t *>(r->centi) : nullptr;
+    size_t i = 0, j = 0;
+    for (long spins = 0;; ++spins) {
+        while (i < B && ws[i] != 0xffffffffu) ++i;
+        while (wc != nullptr && j < B && wc[j] != 0xffffffffu) ++j;
+        if (!first_seen && i > 0) {
+            first_seen = true;
+            r->host_trace[1] = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_ring).count();
+        }
+        if (i == B && (wc == nullptr || j == B)) break;
+        if ((spins & 0x3ff) != 0x3ff) continue;
+        if (std::chrono::steady_clock::now() - t_ring > std::chrono::seconds(5)) {
+            cm::resident_stop(e);
+            r->armed = false;
+            return fail(CM_ERR_CUDA, "resident kernel did not answer within 5 s; disarmed");
+        }
+        if (!resident_alive(r)) {
+            // it left (idle limit) just as the doorbell rang, or it died: a fresh instance picks the doorbell up
+            cudaError_t err = cudaStreamSynchronize(r->stream);
+            if (err != cudaSuccess) return fail(CM_ERR_CUDA, "resident kernel failed: %s", cudaGetErrorString(err));
+            if (int rc = resident_launch(e)) return rc;
+        }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    r->host_trace[2] = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t_ring).count();
+    r->last = door;
+    memcpy(scores, r->scores, B * 4);
+    if (centi) memcpy(centi, r->centi, B * 4);
+    return CM_OK;
+}
+
+}  // namespace
+
+namespace cm {
+
+void resident_stop(cm_engine *e) {
+    cm_resident *r = e->resident;
+    if (r == nullptr || r->stream == nullptr) return;
+    if (resident_alive(r)) {
+        const unsigned long long door = ((unsigned long long)(++r->seq) << 32) | kDoorStop;
+        ring(r, door);
+        r->last = door;
+    }
+    cudaStreamSynchronize(r->stream);
+}
+
+void resident_free(cm_engine *e) {
+    cm_resident *r = e->resident;
+    if (r == nullptr) return;
+    resident_stop(e);
+    if (r->stream) cudaStreamDestroy(r->stream);
+    if (r->d_flag) cudaFree(r->d_flag);
+    if (r->h_block) cudaFreeHost(r->h_block);
+    delete r;
+    e->resident = nullptr;
+}
+
+}  // namespace cm
+
+extern "C" {
+
+int cm_engine_arm_resident(cm_engine *e, int idle_ms) {
+    if (int rc = check_engine(e)) return rc;
+    if (idle_ms < 0 || idle_ms > 10000) return fail(CM_ERR_INVALID, "idle_ms %d outside [0, 10000]", idle_ms);
+    std::lock_guard<std::mutex> lock(e->mu);
+    DeviceGuard guard(e->device);
+    if (e->resident == nullptr) {
+        cm_resident *r = new (std::nothrow) cm_resident();
+        if (r == nullptr) return fail(CM_ERR_NOMEM, "resident state allocation failed");
+        e->resident = r;
+        // records: B * resident_rec_stride(N) ints with B <= kResidentMaxGuesses and B * N <= kResidentMaxRows
+        const size_t off_rec = 256, rec_bytes = ((size_t)kResidentMaxGuesses * (kRecHeaderInts + 7) + kResidentMaxRows + 8) * 4;
+        const size_t off_scores = off_rec + rec_bytes, off_centi = off_scores + (size_t)kResidentMaxGuesses * 4;
+        const size_t bytes = off_centi + (size_t)kResidentMaxGuesses * 4;
+        cudaError_t err = cudaHostAlloc(&r->h_block, bytes, cudaHostAllocDefault);
+        if (err == cudaSuccess) err = cudaMalloc(&r->d_flag, 2 * sizeof(unsigned long long));
+        if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking);
+        if (err != cudaSuccess) {
+            cudaGetLastError();
+            cm::resident_free(e);
+            return fail(CM_ERR_NOMEM, "resident mailbox setup failed: %s", cudaGetErrorString(err));
+        }
+        memset(r->h_block, 0, bytes);
+        r->box = reinterpret_cast<ResidentMailbox *>(r->h_block);
+        r->h_last = reinterpret_cast<unsigned long long *>(r->h_block + 128);
+        r->records = reinterpret_cast<int32_t *>(r->h_block + off_rec);
+        r->scores = reinterpret_cast<float *>(r->h_block + off_scores);
+        r->centi = reinterpret_cast<int32_t *>(r->h_block + off_centi);
+        CM_CUDA(cudaDeviceSynchronize());    // answers registered before arming are complete from here on
+        e->answers_pending = false;
+    }
+    cm_resident *r = e->resident;
+    r->idle_ns = (unsigned long long)(idle_ms == 0 ? 20 : idle_ms) * 1000000ull;
+    r->armed = true;
+    if (!resident_alive(r)) {
+        cudaStreamSynchronize(r->stream);
+        if (int rc = resident_launch(e)) return rc;
+    }
+    return CM_OK;
+}
+
+int cm_engine_disarm_resident(cm_engine *e) {
+    if (int rc = check_engine(e)) return rc;
+    std::lock_guard<std::mutex> lock(e->mu);
+    DeviceGuard guard(e->device);
+    if (e->resident != nullptr) {
+        e->resident->armed = false;
+        cm::resident_stop(e);
+    }
+    return CM_OK;
+}
+
+// Developer aid (CM_RESIDENT_TRACE=1 in the environment before arming): timestamps of the last
+// resident request.  out[0..3] device globaltimer ns: doorbell seen by CTA 0, flag seen by CTA 1, CTA 1
+// scored, CTA 1 has its records staged; out[4..6]: host us from entry to the doorbell, from the doorbell
+// to the first result, from the doorbell to all results.
+int cm_engine_resident_trace(cm_engine *e, double *out7) {
+    if (e == nullptr || out7 == nullptr || e->resident == nullptr) return fail(CM_ERR_INVALID, "no resident state");
+    const unsigned long long *t = reinterpret_cast<const unsigned long long *>(e->resident->h_block + 192);
+    for (int i = 0; i < 4; ++i) out7[i] = (double)t[i];
+    for (int i = 0; i < 3; ++i) out7[4 + i] = e->resident->host_trace[i];
+    return CM_OK;
+}
+
 int cm_score_batch_host(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_len,
                         int n_guesses, int n_slots, const int32_t *answer_slot,
                         const uint8_t *exact, float min_score, float *scores, int32_t *centi) {
@@ -1032,6 +1256,11 @@ int cm_score_batch_host(cm_engine *e, const int32_t *guess_idx, const int32_t *g
     // buffers are first copied into the engine's own pinned block.
     std::lock_guard<std::mutex> lock(e->mu);     // one staging block: callers take turns
     DeviceGuard guard(e->device);
+    // armed and small enough: no launch at all, the resident kernel takes the batch from its mailbox
+    if (e->resident != nullptr && e->resident->armed && n_guesses <= kResidentMaxGuesses &&
+        (int64_t)n_guesses * n_slots <= kResidentMaxRows && min_score == min_score &&
+        ((n_guesses + kResidentCtas - 1) / kResidentCtas) * resident_rec_stride(n_slots) <= kResidentSmemInts)
+        return resident_score(e, guess_idx, guess_len, n_guesses, n_slots, answer_slot, exact, min_score, scores, centi);
     const size_t B = (size_t)n_guesses, N = (size_t)n_slots;
     const bool in_pinned = is_pinned_host(guess_idx) && is_pinned_host(guess_len) &&
                            is_pinned_host(answer_slot) && (!exact || is_pinned_host(exact));

@@ -83,6 +83,15 @@ class ScoringEngine:
     def synchronize(self) -> None:
         check(self._lib.cm_engine_synchronize(self._h))
 
+    def arm_resident(self, idle_ms: int = 0) -> None:
+        """Keep a small kernel resident so that ``score_host`` on micro-batches (<= 1024 guesses,
+        <= 4096 words) needs no launch: the batch goes through a page-locked mailbox.  The kernel
+        leaves after ``idle_ms`` (0 = 20 ms) without work and is re-launched on demand."""
+        check(self._lib.cm_engine_arm_resident(self._h, int(idle_ms)))
+
+    def disarm_resident(self) -> None:
+        check(self._lib.cm_engine_disarm_resident(self._h))
+
     # ---- answers ---------------------------------------------------------------------
     def _stream(self, stream: Optional[int]) -> int:
         # None = the engine's own stream; an int (0 included: CUDA's default stream) is used as is

@@ -126,6 +126,25 @@ int cm_score_batch_host(cm_engine *e,
                         const int32_t *answer_slot, const uint8_t *exact,
                         float min_score, float *scores, int32_t *centi);
 
+/* Resident kernel for micro-batches.  No reference counterpart: the reference scores a request's
+ * two words inline (src/backend.py:312-317); this serves BASELINE configs[1], many small
+ * concurrent requests coalesced by the micro-batcher, whose metric is latency.  One blocking
+ * cm_score_batch_host call for a few hundred guesses spends most of its time launching a 4 us
+ * kernel and synchronising with it.  After cm_engine_arm_resident the engine keeps a small
+ * kernel resident (one 128-thread CTA per SM, idle at low duty) that polls a doorbell in
+ * page-locked memory: cm_score_batch_host then packs the batch into the mailbox, rings, and
+ * watches the results arrive -- two PCIe crossings, no launch.  Used for calls with
+ * n_guesses <= 1024 and n_guesses * n_slots <= 4096 (where it is measured to win); larger ones
+ * take the launch path as before; results are bit-identical either way.
+ * The kernel leaves by itself after `idle_ms` (0 = 20 ms) without a request and is launched
+ * again by the next small call, so anything in the process that synchronises the whole device
+ * (cudaFree, cudaDeviceSynchronize) waits at most that long for it.  cm_engine_upload_rows and
+ * cm_engine_fill_synthetic stop it first.  cm_engine_disarm_resident stops it and returns
+ * cm_score_batch_host to the launch path; cm_engine_destroy does so too.                       */
+int cm_engine_arm_resident(cm_engine *e, int idle_ms);
+int cm_engine_disarm_resident(cm_engine *e);
+int cm_engine_resident_trace(cm_engine *e, double *out7);   /* developer aid, see cm_scorer.cu */
+
 /* ---- pipelined host path --------------------------------------------------------------- *
  * No reference counterpart: the reference scores one request at a time inside its event
  * loop (src/backend.py:312-317).  This is the device half of the request micro-batcher that
