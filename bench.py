@@ -432,7 +432,8 @@ def run_own(args) -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    flush_buf = torch.zeros(512 << 20, dtype=torch.uint8, device=dev)
+    flush_sink = torch.zeros((), dtype=torch.int64, device=dev)
     align_t = torch.zeros(1, dtype=torch.float32, device=dev)
 
     def timed_steps(first: int, count: int):
@@ -441,12 +442,13 @@ def run_own(args) -> None:
         barrier()
         # Still outside the timed region, on the launch stream: (several GPUs) a one-element all-reduce,
         # which every rank's stream leaves at the same moment, so the ranks' regions start together
-        # instead of a host-barrier's skew apart; then an L2 flush (a write larger than the 126 MB L2),
-        # behind which the K launches queue up -- the region between the two events then holds K steps
+        # instead of a host-barrier's skew apart; then an L2 flush (a read four times the 126 MB L2; a
+        # write would leave 126 MB of dirty lines for the first timed steps to evict), behind which the
+        # K launches queue up -- the region between the two events then holds K steps
         # of device work and not the first launch's latency (K = 20 is a 0.25 ms region).
         if world > 1:
             dist.all_reduce(align_t)
-        flush_buf.zero_()
+        flush_sink.copy_(torch.count_nonzero(flush_buf))     # a READ of 512 MB: L2 is left full of clean lines
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         t_h = time.perf_counter()
@@ -998,7 +1000,7 @@ def run_own(args) -> None:
                        "gather_verified": gather_check, "gather_verified_steps": gather_steps,
                        "cpus_near_gpu": near_cpus,
                        "steps_enqueued_by": "cm_score_batch_list_device, one C-ABI call per <= 64 steps",
-                       "l2": f"ring of {RING} distinct batches over a 3.6 GB table (inputs >> L2); a 256 MB write "
+                       "l2": f"ring of {RING} distinct batches over a 3.6 GB table (inputs >> L2); a 512 MB read "
                              f"flushes L2 right before the first event of the timed region"},
             "sustained": sustained,
             "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
