@@ -49,7 +49,8 @@ def needs_build() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB_PATH
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) \
+    extra = os.environ.get("CM_NVCC_EXTRA", "").split()      # developer aid: e.g. -DSOME_EXPERIMENT
+    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) \
         + ["-I", INCLUDE, "-o", LIB_PATH] + sources()
     subprocess.check_call(cmd)
     return LIB_PATH
