@@ -435,6 +435,14 @@ def run_own(args) -> None:
     flush_buf = torch.zeros(512 << 20, dtype=torch.uint8, device=dev)
     flush_sink = torch.zeros((), dtype=torch.int64, device=dev)
     align_t = torch.zeros(1, dtype=torch.float32, device=dev)
+    # once now, so that the caching allocator holds the reduction's workspace and the communicator has
+    # seen this stream: a first-call cudaMalloc on one rank's host between the alignment and the timed
+    # launches is milliseconds that every other rank's ship CTA then waits for
+    for _ in range(2):
+        flush_sink.copy_(torch.count_nonzero(flush_buf))
+        if world > 1:
+            dist.all_reduce(align_t)
+    torch.cuda.synchronize()
 
     def timed_steps(first: int, count: int):
         """`count` steps between two events on the launch stream, a barrier + synchronize on both
