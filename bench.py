@@ -573,6 +573,12 @@ def run_own(args) -> None:
         per_step_ms = max(dev_ms / args.steps, 1e-3)
         n_roof = int(min(200_000, max(2000, args.roofline_s * 1e3 / per_step_ms)))
         kern_us = kernel_time_us(kernel_list, n_roof)
+        kern_us_ranks = None
+        if world > 1:          # the same launches on every GPU at once, no exchange: how far apart the GPUs themselves are
+            t_k = torch.tensor([kern_us], dtype=torch.float64, device=dev)
+            all_k = [torch.zeros_like(t_k) for _ in range(world)]
+            dist.all_gather(all_k, t_k)
+            kern_us_ranks = [float(x.item()) for x in all_k]
         # launch i used ring batch i % RING: the bytes those launches needed, averaged per launch
         visits = np.bincount(np.arange(n_roof) % RING, minlength=RING)
         rows_per_launch = float(np.dot(visits, ring_rows)) / n_roof
@@ -587,7 +593,7 @@ def run_own(args) -> None:
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                     "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                     "kernel": "cm_score_kernel<VPL=5,LPG=16,R=1> (4096x16 launches, CM_SCORE_OVERLAP_PREVIOUS)",
-                    "kernel_us": kern_us, "launches_timed": n_roof,
+                    "kernel_us": kern_us, "launches_timed": n_roof, "kernel_us_per_rank": kern_us_ranks,
                     "algorithmic_bytes_per_launch": need,
                     "bytes_model": "1200 B x rows of live guesses (no rows for unknown words, exact matches, unknown "
                                    "answers) + 4 B per index + 8 B of length/slot/score per guess",
@@ -722,6 +728,17 @@ def run_own(args) -> None:
         one_s = max_over_ranks(time.perf_counter() - t0)
         e2e["one_step_per_call"] = {"value": n_long_e * B * world / one_s, "unit": UNIT, "steps": n_long_e,
                                     "ms_per_step": one_s / n_long_e * 1e3, "api": "cm_pipe_cycle, one call per step"}
+        # the ceiling of this figure: the same copies with no kernel at all, every rank at once -- what the
+        # host and the PCIe path sustain (several GPUs share one host's memory system and PCIe switches)
+        secs = ctypes.c_double(0.0)
+        n_probe = 4000
+        barrier()
+        _lib.check(lib.cm_pipe_probe_copies(pipe_dma._h, n_probe, PIPE_DEPTH, ctypes.byref(secs)))
+        probe_s = max_over_ranks(secs.value)
+        e2e["pcie_ceiling"] = {"value": n_probe * B * world / probe_s, "unit": UNIT, "ms_per_step": probe_s / n_probe * 1e3,
+                               "gbs_per_gpu": (h2d + B * 4) / (probe_s / n_probe) / 1e9,
+                               "note": "H2D copy of a step's inputs + D2H copy of its scores per step through the "
+                                       "copy engine, no kernel, all ranks at once (cm_pipe_probe_copies)"}
         # (a'') the same call pinned to each route (the pipe itself times both as it runs and keeps
         #       the faster one: which one wins depends on how busy the PCIe path is)
         for tag, pp, vv, note in (("copy_engine_route", pipe_dma, views_dma, "CM_PIPE_ROUTE=copy: H2D DMA, kernel, D2H DMA per step"),

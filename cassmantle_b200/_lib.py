@@ -61,6 +61,7 @@ _SIGNATURES = {
     "cm_pipe_wait": (_c.c_int, [_P, _c.c_int]),
     "cm_pipe_cycle": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_float, _c.c_int]),
     "cm_pipe_cycle_many": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.c_int, _c.c_float, _c.c_int]),
+    "cm_pipe_probe_copies": (_c.c_int, [_P, _c.c_int, _c.c_int, _c.POINTER(_c.c_double)]),
     "cm_vocab_create": (_c.c_int, [_c.POINTER(_P), _P, _P, _P, _c.c_int64]),
     "cm_vocab_destroy": (_c.c_int, [_P]),
     "cm_vocab_size": (_c.c_int, [_P, _c.POINTER(_c.c_int64), _c.POINTER(_c.c_int64)]),

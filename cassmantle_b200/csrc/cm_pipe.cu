@@ -233,6 +233,32 @@ int cm_pipe_cycle_many(cm_pipe *p, int wait_first, int submit_first, int count, 
     return CM_OK;
 }
 
+// Developer aid / measurement: the copy-engine route of `steps` steps WITHOUT the kernel -- H2D copy of
+// the slot's inputs, D2H copy of its scores, `in_flight` slots busy at a time -- so that a caller can
+// tell what the host and the PCIe path alone sustain (bench.py reports it as the ceiling of the
+// end-to-end figure when several GPUs share one host).  Slots must have been sized with cm_pipe_buffers.
+int cm_pipe_probe_copies(cm_pipe *p, int steps, int in_flight, double *seconds) {
+    if (p == nullptr || seconds == nullptr) return fail(CM_ERR_INVALID, "NULL argument");
+    const int depth = (int)p->slots.size();
+    if (in_flight < 1 || in_flight > depth) return fail(CM_ERR_INVALID, "in_flight %d outside [1, %d]", in_flight, depth);
+    cm::DeviceGuard guard(p->engine->device);
+    for (auto &s : p->slots)
+        if (s.in_flight || s.n_guesses < 1) return fail(CM_ERR_STATE, "every slot must be sized and idle");
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int i = 0; i < steps; ++i) {
+        cm_pipe_slot &s = p->slots[i % depth];
+        if (i >= in_flight) CM_CUDA(cudaEventSynchronize(p->slots[(i - in_flight) % depth].done));
+        CM_CUDA(cudaMemcpyAsync(s.d, s.h, s.in_bytes, cudaMemcpyHostToDevice, s.stream));
+        CM_CUDA(cudaMemcpyAsync(s.h + s.off_scores, s.d + s.off_scores, (size_t)s.n_guesses * 4,
+                                cudaMemcpyDeviceToHost, s.stream));
+        CM_CUDA(cudaEventRecord(s.done, s.stream));
+    }
+    for (int i = steps > in_flight ? steps - in_flight : 0; i < steps; ++i)
+        CM_CUDA(cudaEventSynchronize(p->slots[i % depth].done));
+    *seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return CM_OK;
+}
+
 int cm_pipe_depth(cm_pipe *p) { return p ? (int)p->slots.size() : 0; }
 
 }  // extern "C"

@@ -179,6 +179,10 @@ int cm_pipe_cycle(cm_pipe *p, int wait_slot, int submit_slot, float min_score, i
  * wait_first < 0: no waits; submit_first < 0: no submits.  count <= depth.                  */
 int cm_pipe_cycle_many(cm_pipe *p, int wait_first, int submit_first, int count, float min_score,
                        int want_centi);
+/* Measurement aid: `steps` steps of the copy-engine route with the kernel left out (H2D copy of the
+ * slot's inputs, D2H copy of its scores, `in_flight` slots busy at a time); *seconds receives the wall
+ * time.  What the host and the PCIe path alone sustain -- the ceiling of the pipelined figure.      */
+int cm_pipe_probe_copies(cm_pipe *p, int steps, int in_flight, double *seconds);
 
 /* ---- vocabulary lookup on the device -------------------------------- *
  * Replaces `inputs.lower()` (src/backend.py:304) + gensim's `key_to_index[word]` dict lookup
