@@ -696,6 +696,7 @@ def run_own(args) -> None:
         # untimed: the usual warm-up plus the pipe's own route trial (64 + 2 x 288 submits), so that
         # the timed steps run on the route it settled on, as a long-running server's would
         pipe_warmup = max(args.warmup, PIPE_DEPTH, 700)
+        barrier()            # every rank's route trial under the same load: all ranks on the PCIe path at once
         run_pipe(0, pipe_warmup)
         barrier()
         launches1 = lib.cm_kernel_launch_count()
