@@ -53,6 +53,9 @@ _SIGNATURES = {
     "cm_engine_arm_resident": (_c.c_int, [_P, _c.c_int]),
     "cm_engine_disarm_resident": (_c.c_int, [_P]),
     "cm_engine_resident_trace": (_c.c_int, [_P, _P]),
+    "cm_score_batch_device_idx24": (_c.c_int, [_P, _P, _P, _c.c_int, _c.c_int, _P, _P, _c.c_float,
+                                               _P, _P, _c.c_uint32, _P]),
+    "cm_pipe_set_idx24": (_c.c_int, [_P, _c.c_int]),
     "cm_pipe_create": (_c.c_int, [_c.POINTER(_P), _P, _c.c_int, _c.c_int, _c.c_int]),
     "cm_pipe_destroy": (_c.c_int, [_P]),
     "cm_pipe_depth": (_c.c_int, [_P]),

@@ -75,6 +75,6 @@ void resident_free(cm_engine *e);
 int enqueue_score(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_len, int n_guesses,
                   int n_slots, const int32_t *answer_slot, const uint8_t *exact, float min_score,
                   float *scores, int32_t *centi, uint32_t flags, cudaStream_t st,
-                  const ShipArgs *ship = nullptr);
+                  const ShipArgs *ship = nullptr, bool idx24 = false);   // idx24: guess_idx holds 3-byte indices
 
 }  // namespace cm

@@ -42,6 +42,7 @@ struct cm_pipe {
     size_t direct_in_max = 0;       // inputs up to this many bytes are read in place by the kernel
     int direct_out_max = 0;         // up to this many guesses the kernel writes scores in place
     cm::RouteTuner tuner;           // mid-size batches (kSmallIn < inputs <= direct_in_max): cm_route_tuner.h
+    bool idx24 = false;             // slots hold 3-byte indices (cm_pipe_set_idx24)
 };
 
 namespace {
@@ -49,8 +50,8 @@ namespace {
 using cm::align_up;
 using cm::fail;
 
-void layout(cm_pipe_slot &s, size_t B, size_t N) {
-    s.off_len = align_up(B * N * 4, 16);
+void layout(cm_pipe_slot &s, size_t B, size_t N, bool idx24) {
+    s.off_len = align_up(B * N * (idx24 ? 3 : 4), 16);
     s.off_slot = s.off_len + align_up(B * 4, 16);
     s.off_exact = s.off_slot + align_up(B * 4, 16);
     s.in_bytes = align_up(s.off_exact + B, 256);
@@ -118,7 +119,7 @@ int cm_pipe_create(cm_pipe **out, cm_engine *e, int depth, int max_guesses, int 
     p->max_guesses = max_guesses;
     p->max_slots = max_slots;
     cm_pipe_slot probe;
-    layout(probe, (size_t)max_guesses, (size_t)max_slots);
+    layout(probe, (size_t)max_guesses, (size_t)max_slots, false);
     p->slot_bytes = probe.off_centi + align_up((size_t)max_guesses * 4, 256);
     p->slots.resize(depth);
     p->direct_in_max = env_size("CM_PIPE_DIRECT_IN_MAX", kDirectInMax);
@@ -146,6 +147,17 @@ int cm_pipe_create(cm_pipe **out, cm_engine *e, int depth, int max_guesses, int 
     return CM_OK;
 }
 
+int cm_pipe_set_idx24(cm_pipe *p, int on) {
+    if (p == nullptr) return fail(CM_ERR_INVALID, "pipe is NULL");
+    for (auto &s : p->slots)
+        if (s.in_flight) return fail(CM_ERR_STATE, "a slot is in flight");
+    if (on && p->engine->n_rows > 0xffffffLL)
+        return fail(CM_ERR_INVALID, "3-byte indices need a table of at most 16,777,215 rows");
+    p->idx24 = on != 0;
+    for (auto &s : p->slots) s.n_guesses = 0;            // layouts change: cm_pipe_buffers must be called again
+    return CM_OK;
+}
+
 int cm_pipe_buffers(cm_pipe *p, int slot, int n_guesses, int n_slots, int32_t **guess_idx,
                     int32_t **guess_len, int32_t **answer_slot, uint8_t **exact, float **scores,
                     int32_t **centi) {
@@ -158,7 +170,7 @@ int cm_pipe_buffers(cm_pipe *p, int slot, int n_guesses, int n_slots, int32_t **
     if (s.in_flight) return fail(CM_ERR_STATE, "slot %d is in flight; cm_pipe_wait it first", slot);
     s.n_guesses = n_guesses;
     s.n_slots = n_slots;
-    layout(s, (size_t)n_guesses, (size_t)n_slots);
+    layout(s, (size_t)n_guesses, (size_t)n_slots, p->idx24);
     if (guess_idx) *guess_idx = (int32_t *)s.h;
     if (guess_len) *guess_len = (int32_t *)(s.h + s.off_len);
     if (answer_slot) *answer_slot = (int32_t *)(s.h + s.off_slot);
@@ -184,7 +196,8 @@ int cm_pipe_submit(cm_pipe *p, int slot, float min_score, int want_centi) {
     if (int rc = cm::enqueue_score(e, (const int32_t *)in, (const int32_t *)(in + s.off_len),
                                    s.n_guesses, s.n_slots, (const int32_t *)(in + s.off_slot),
                                    in + s.off_exact, min_score, (float *)(res + s.off_scores),
-                                   want_centi ? (int32_t *)(res + s.off_centi) : nullptr, 0u, s.stream))
+                                   want_centi ? (int32_t *)(res + s.off_centi) : nullptr, 0u, s.stream,
+                                   nullptr, p->idx24))
         return rc;
     if (!direct_out) {
         const size_t n = want_centi ? s.off_centi + (size_t)s.n_guesses * 4 - s.off_scores

@@ -174,7 +174,21 @@ cm_answer_unit_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
 // has staged in shared memory, and the answers -- rewritten by cm_set_answers while the kernel is
 // resident -- are read with L2-only loads, issued before the gather (a micro-batch is a latency
 // chain, not bandwidth).  SYS = false: the launched kernels, packed arrays.
-template <int VPL, int LPG, int R, bool STREAM, int THREADS, bool SINGLE, bool SYS = false>
+// IDX24: guess_idx is really an array of 3-byte little-endian row numbers (0xFFFFFF = not in the
+// vocabulary), the packed form the pipelined host path can take: a quarter fewer input bytes per
+// guess across PCIe, which is what bounds eight GPUs behind one host.
+template <bool IDX24>
+__device__ __forceinline__ int32_t ld_idx(const int32_t *base, size_t k) {
+    if constexpr (IDX24) {
+        const uint8_t *p = reinterpret_cast<const uint8_t *>(base) + 3 * k;
+        const uint32_t v = (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16);
+        return v == 0xffffffu ? -1 : (int32_t)v;
+    } else {
+        return base[k];
+    }
+}
+
+template <int VPL, int LPG, int R, bool STREAM, int THREADS, bool SINGLE, bool SYS = false, bool IDX24 = false>
 __device__ __forceinline__ void
 score_groups(int warp, const float *__restrict__ table, int64_t n_rows, int dim4,
              const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
@@ -201,7 +215,7 @@ score_groups(int warp, const float *__restrict__ table, int64_t n_rows, int dim4
     // ---- phase 0: independent loads, one DRAM round trip ---------------------------------
     // SYS: guess b is one record of rec_stride ints, {len, slot, exact, index 0, index 1, ...}, which
     // guess_len points at (guess_idx points at its fourth int); shared memory, broadcast reads.
-    const int32_t *gi = guess_idx + (size_t)b * (SYS ? rec_stride : n_slots);
+    const size_t g0 = (size_t)b * (SYS ? rec_stride : n_slots);       // first index of guess b
     bool is_exact;
     int n, slot;
     if constexpr (SYS) {
@@ -215,7 +229,7 @@ score_groups(int warp, const float *__restrict__ table, int64_t n_rows, int dim4
         slot = answer_slot[b];
     }
     // SINGLE (n_slots == 1, the reference's own shape): every lane of the group reads the one index
-    int32_t mine = SINGLE ? gi[0] : ((sub < n_slots) ? gi[sub] : -1);
+    int32_t mine = SINGLE ? ld_idx<IDX24>(guess_idx, g0) : ((sub < n_slots) ? ld_idx<IDX24>(guess_idx, g0 + sub) : -1);
     n = n < 0 ? 0 : (n > n_slots ? n_slots : n);
     const bool slot_ok = slot >= 0 && slot < n_answers;
 
@@ -226,7 +240,7 @@ score_groups(int warp, const float *__restrict__ table, int64_t n_rows, int dim4
     } else {
         bad = (sub < n) && (mine < 0 || (int64_t)mine >= n_rows);
         for (int c = LPG + sub; c < n; c += LPG) {
-            const int32_t r = gi[c];
+            const int32_t r = ld_idx<IDX24>(guess_idx, g0 + c);
             bad |= (r < 0) || ((int64_t)r >= n_rows);
         }
         const unsigned gmask = (LPG == 32) ? cm::kFullMask : (((1u << LPG) - 1u) << grp_base);
@@ -264,7 +278,7 @@ score_groups(int warp, const float *__restrict__ table, int64_t n_rows, int dim4
         }
     } else
     for (int c = 0; c < n_max; c += LPG) {
-        if (c > 0) mine = (c + sub < n_live) ? gi[c + sub] : 0;
+        if (c > 0) mine = (c + sub < n_live) ? ld_idx<IDX24>(guess_idx, g0 + c + sub) : 0;
         const int m = min(LPG, n_max - c);
         for (int k = 0; k < m; k += R) {
             float4 buf[R][VPL];
@@ -338,7 +352,7 @@ score_groups(int warp, const float *__restrict__ table, int64_t n_rows, int dim4
     }
 }
 
-template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE>
+template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE, bool IDX24>
 __global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
 cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
                 const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
@@ -356,7 +370,7 @@ cm_score_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
         cm::ship_duty(ship, (int)blockIdx.x, n_ship_ctas);
         return;
     }
-    score_groups<VPL, LPG, R, STREAM, THREADS, SINGLE>(
+    score_groups<VPL, LPG, R, STREAM, THREADS, SINGLE, false, IDX24>(
         ((int)blockIdx.x - n_ship_ctas) * (THREADS / 32) + (int)(threadIdx.x >> 5),
         table, n_rows, dim4, guess_idx, guess_len, n_guesses, n_slots, ans_unit, ans_rows, n_answers,
         answer_slot, exact, min_score, scores, centi, flags);
@@ -620,7 +634,7 @@ namespace {
 // (environment, read once) overrides only the shape heuristic, for A/B timing of these four.
 enum ScoreKernel { kAuto = 0, kWide, kPaired, kSingle, kPersistent };
 
-template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE = false>
+template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE = false, bool IDX24 = false>
 void launch_variant(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
                     const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
                     int32_t *centi, uint32_t flags, cudaStream_t st, const cm::ShipArgs *ship) {
@@ -637,7 +651,7 @@ void launch_variant(const cm_engine *e, const int32_t *gi, const int32_t *gl, in
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaLaunchKernelEx(&cfg, cm_score_kernel<VPL, LPG, R, STREAM, THREADS, MIN_BLOCKS, SINGLE>,
+    cudaLaunchKernelEx(&cfg, cm_score_kernel<VPL, LPG, R, STREAM, THREADS, MIN_BLOCKS, SINGLE, IDX24>,
                        (const float *)e->d_table, e->n_rows, e->dim / 4, gi, gl, B, N,
                        (const float *)e->d_ans_unit, (const int32_t *)e->d_ans_rows, e->n_answers,
                        slot, exact, min_score, scores, centi, flags, n_ship_ctas,
@@ -685,14 +699,14 @@ ScoreKernel forced_kernel() {
     return v;
 }
 
-template <int VPL>
+template <int VPL, bool IDX24 = false>
 void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
                   const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
                   int32_t *centi, uint32_t flags, cudaStream_t st, const cm::ShipArgs *ship = nullptr) {
 #define CM_V(LPG, R, STREAM, THREADS, MINB, VP) \
-    launch_variant<VP, LPG, R, STREAM, THREADS, MINB>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st, ship)
+    launch_variant<VP, LPG, R, STREAM, THREADS, MINB, false, IDX24>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st, ship)
 #define CM_S(LPG, STREAM, THREADS, MINB, VP) \
-    launch_variant<VP, LPG, 1, STREAM, THREADS, MINB, true>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st, ship)
+    launch_variant<VP, LPG, 1, STREAM, THREADS, MINB, true, IDX24>(e, gi, gl, B, N, slot, exact, min_score, scores, centi, flags, st, ship)
     if constexpr (VPL == 3) {
         if (e->dim == 300) {
             // Measured on B200 (tools/probe_kernel.py, us per launch, CM_SCORE_OVERLAP_PREVIOUS):
@@ -703,8 +717,12 @@ void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int 
             if (k == kAuto)
                 k = (N == 1) ? (B > (1 << 18) ? kPersistent : kSingle)
                              : ((int64_t)B * N >= 32768 ? kPaired : kWide);
+            if (IDX24 && k == kPersistent) k = kSingle;          // the persistent form takes 4-byte indices only
             switch (k) {
-                case kPersistent: launch_single_persistent<10, 8, true, 128, 6>(e, gi, gl, B, slot, exact, min_score, scores, centi, flags, st, ship); return;
+                case kPersistent:
+                    if constexpr (!IDX24)
+                        launch_single_persistent<10, 8, true, 128, 6>(e, gi, gl, B, slot, exact, min_score, scores, centi, flags, st, ship);
+                    return;
                 case kSingle: CM_S(8, true, 128, 8, 10); return;
                 case kPaired: CM_V(16, 1, true, 128, 7, 5); return;
                 default: CM_V(32, 2, true, 128, 8, 3); return;
@@ -757,8 +775,12 @@ bool is_pinned_host(const void *p) {
 
 int enqueue_score(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_len, int n_guesses,
                   int n_slots, const int32_t *answer_slot, const uint8_t *exact, float min_score,
-                  float *scores, int32_t *centi, uint32_t flags, cudaStream_t st, const ShipArgs *ship) {
+                  float *scores, int32_t *centi, uint32_t flags, cudaStream_t st, const ShipArgs *ship,
+                  bool idx24) {
     if (int rc = check_engine(e)) return rc;
+    if (idx24 && e->n_rows > 0xffffffLL)
+        return fail(CM_ERR_INVALID, "3-byte indices need a table of at most 16,777,215 rows, this one has %lld",
+                    (long long)e->n_rows);
     if (n_guesses < 0) return fail(CM_ERR_INVALID, "n_guesses %d is negative", n_guesses);
     if (n_slots < 1 || n_slots > CM_MAX_SEQ)
         return fail(CM_ERR_INVALID, "n_slots %d outside [1, %d]", n_slots, CM_MAX_SEQ);
@@ -769,10 +791,17 @@ int enqueue_score(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_l
         return fail(CM_ERR_INVALID, "a required buffer pointer is NULL");
     if (e->n_answers < 1) return fail(CM_ERR_STATE, "cm_set_answers has not been called");
     DeviceGuard guard(e->device);
+    if (idx24) {
+#define CM_CALL(V) launch_score<V, true>(e, guess_idx, guess_len, n_guesses, n_slots, answer_slot, exact, \
+                                         min_score, scores, centi, flags, st, ship)
+        CM_DISPATCH_VPL(e->dim, CM_CALL)
+#undef CM_CALL
+    } else {
 #define CM_CALL(V) launch_score<V>(e, guess_idx, guess_len, n_guesses, n_slots, answer_slot, exact, \
                                    min_score, scores, centi, flags, st, ship)
-    CM_DISPATCH_VPL(e->dim, CM_CALL)
+        CM_DISPATCH_VPL(e->dim, CM_CALL)
 #undef CM_CALL
+    }
     CM_CUDA(cudaGetLastError());
     return CM_OK;
 }
@@ -1237,6 +1266,15 @@ int cm_engine_resident_trace(cm_engine *e, double *out7) {
     for (int i = 0; i < 4; ++i) out7[i] = (double)t[i];
     for (int i = 0; i < 3; ++i) out7[4 + i] = e->resident->host_trace[i];
     return CM_OK;
+}
+
+int cm_score_batch_device_idx24(cm_engine *e, const uint8_t *d_guess_idx24, const int32_t *d_guess_len,
+                                int n_guesses, int n_slots, const int32_t *d_answer_slot,
+                                const uint8_t *d_exact, float min_score, float *d_scores,
+                                int32_t *d_centi, uint32_t flags, void *stream) {
+    return cm::enqueue_score(e, reinterpret_cast<const int32_t *>(d_guess_idx24), d_guess_len, n_guesses, n_slots,
+                             d_answer_slot, d_exact, min_score, d_scores, d_centi, flags, (cudaStream_t)stream,
+                             nullptr, true);
 }
 
 int cm_score_batch_host(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_len,

@@ -156,6 +156,14 @@ class ScoringEngine:
             flags, self._stream(stream) or None))
 
 
+def pack_idx24(idx: np.ndarray) -> np.ndarray:
+    """int32 row numbers [..., N] (-1 = not in the vocabulary) -> uint8 [..., N, 3], little-endian,
+    0xFFFFFF for -1: the packed index form of ``ScoringPipe(packed=True)`` / cm_pipe_set_idx24."""
+    a = np.asarray(idx, dtype=np.int32)
+    u = np.ascontiguousarray(np.where(a < 0, -1, a)).view(np.uint32)     # -1 -> 0xFFFFFFFF -> low 3 bytes 0xFFFFFF
+    return np.ascontiguousarray(u[..., None].view(np.uint8)[..., :3])
+
+
 class ScoringPipe:
     """Ring of page-locked batch slots on one engine (C ABI: cm_pipe_*).
 
@@ -166,12 +174,15 @@ class ScoringPipe:
     """
 
     def __init__(self, engine: ScoringEngine, depth: int = 4, max_guesses: int = 4096,
-                 max_slots: int = 16) -> None:
+                 max_slots: int = 16, packed: bool = False) -> None:
         self._lib = engine._lib
         self.engine = engine
         self._h = ctypes.c_void_p()
         check(self._lib.cm_pipe_create(ctypes.byref(self._h), engine._h, depth, max_guesses, max_slots))
         self.depth = depth
+        self.packed = bool(packed)      # 3-byte indices in the slots: ``guess_idx`` views are uint8 [B, N, 3]
+        if self.packed:
+            check(self._lib.cm_pipe_set_idx24(self._h, 1))
 
     def close(self) -> None:
         if getattr(self, "_h", None) is not None and self._h.value:
@@ -195,7 +206,8 @@ class ScoringPipe:
 
         B, N = n_guesses, n_slots
         return {
-            "guess_idx": view(ptrs[0], ctypes.c_int32, (B, N)),
+            "guess_idx": (view(ptrs[0], ctypes.c_uint8, (B, N, 3)) if self.packed
+                          else view(ptrs[0], ctypes.c_int32, (B, N))),
             "guess_len": view(ptrs[1], ctypes.c_int32, (B,)),
             "answer_slot": view(ptrs[2], ctypes.c_int32, (B,)),
             "exact": view(ptrs[3], ctypes.c_uint8, (B,)),

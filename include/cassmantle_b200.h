@@ -114,6 +114,16 @@ int cm_score_batch_device(cm_engine *e,
                           float min_score, float *d_scores, int32_t *d_centi,
                           uint32_t flags, void *stream);
 
+/* The same with 3-byte indices (little-endian row number, 0xFFFFFF = not in the vocabulary): the
+ * packed form that the pipelined host path ships across PCIe (cm_pipe_set_idx24).  Tables of at most
+ * 16,777,215 rows; the word2vec table (download_model.py:9) has 3,000,000.                          */
+int cm_score_batch_device_idx24(cm_engine *e,
+                                const uint8_t *d_guess_idx24, const int32_t *d_guess_len,
+                                int n_guesses, int n_slots,
+                                const int32_t *d_answer_slot, const uint8_t *d_exact,
+                                float min_score, float *d_scores, int32_t *d_centi,
+                                uint32_t flags, void *stream);
+
 /* Same call with HOST buffers: stages the inputs to the GPU, scores, copies the results
  * back and returns when `scores` (and `centi`, if not NULL) are valid.  This is what the
  * Python boundary (cassmantle_b200/backend.py) calls per micro-batch.  Page-locked
@@ -170,6 +180,12 @@ int cm_pipe_depth(cm_pipe *p);
 int cm_pipe_buffers(cm_pipe *p, int slot, int n_guesses, int n_slots,
                     int32_t **guess_idx, int32_t **guess_len, int32_t **answer_slot,
                     uint8_t **exact, float **scores, int32_t **centi);
+/* Packed indices: after cm_pipe_set_idx24(p, 1) the guess_idx block of every slot holds 3 bytes per
+ * index, little-endian, 0xFFFFFF = not in the vocabulary (cm_pipe_buffers still returns it through
+ * the int32_t** argument: treat it as uint8_t[n_guesses * n_slots * 3]).  Same scores; a quarter fewer
+ * input bytes per guess across PCIe, which is what bounds several GPUs behind one host.  Tables of at
+ * most 16,777,215 rows.  Call cm_pipe_buffers again afterwards.                                    */
+int cm_pipe_set_idx24(cm_pipe *p, int on);
 int cm_pipe_submit(cm_pipe *p, int slot, float min_score, int want_centi);
 int cm_pipe_wait(cm_pipe *p, int slot);
 /* cm_pipe_wait(wait_slot) (skipped when wait_slot < 0) followed by cm_pipe_submit(submit_slot). */

@@ -183,6 +183,63 @@ def test_batch_list_entry_point_equals_single_calls(small_engine):
     assert lib.cm_score_batch_list_device(small_engine._h, None, None, 0, ctypes.c_float(0.01), 0, st) == 0
 
 
+@pytest.mark.parametrize("B,N", [(4096, 16), (512, 8), (3000, 1), (100, 100), (2500, 40), (1, 1)])
+def test_packed_24_bit_indices_equal_32_bit_indices(small_engine, B, N):
+    """cm_score_batch_device_idx24: 3-byte indices (0xFFFFFF = unknown word), same bits out."""
+    import ctypes
+    import torch
+    from cassmantle_b200 import _lib
+    from cassmantle_b200.engine import pack_idx24
+    lib = _lib.load()
+    dev = torch.device("cuda:0")
+    idx, ln, ans, slot, ex = synth.make_guess_batch(B, N, 50_000, 3, seed=B + N, ragged=N > 1, oov_frac=0.2)
+    idx[0, 0] = 49_999                                        # the last row of the table
+    small_engine.set_answers(ans)
+    want, want_c = small_engine.score_host(idx, ln, slot, ex, 0.01, want_centi=True)
+    packed = pack_idx24(idx)
+    assert packed.shape == (B, N, 3) and packed[idx < 0].min(initial=255) == 255
+    t = [torch.from_numpy(a).to(dev) for a in (packed, ln, slot, ex)]
+    out = torch.full((B,), -3.0, dtype=torch.float32, device=dev)
+    cen = torch.full((B,), -3, dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    rc = lib.cm_score_batch_device_idx24(small_engine._h, t[0].data_ptr(), t[1].data_ptr(), B, N, t[2].data_ptr(),
+                                         t[3].data_ptr(), ctypes.c_float(np.float32(0.01)), out.data_ptr(),
+                                         cen.data_ptr(), 0, st)
+    assert rc == 0, lib.cm_last_error()
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(cen.cpu().numpy(), want_c)
+
+
+@pytest.mark.parametrize("route", ["inplace", "copy"])
+def test_pipe_with_packed_indices(small_engine, monkeypatch, route):
+    """cm_pipe_set_idx24: the slots carry 3 bytes per index on both routes; scores as the 32-bit pipe's."""
+    from cassmantle_b200.engine import ScoringPipe, pack_idx24
+    monkeypatch.setenv("CM_PIPE_ROUTE", route)
+    ans = np.array([7, 4242, 31337], np.int32)
+    small_engine.set_answers(ans)
+    small_engine.synchronize()
+    pipe = ScoringPipe(small_engine, depth=3, max_guesses=4096, max_slots=16, packed=True)
+    shapes = [(4096, 16), (100, 1), (777, 5), (4096, 12), (1, 16)]
+    for rep in range(2):
+        for i, (B, N) in enumerate(shapes):
+            idx, ln, _, slot, ex = synth.make_guess_batch(B, N, 50_000, 3, seed=600 + i, ragged=N > 1, oov_frac=0.1)
+            want = small_engine.score_host(idx, ln, slot, ex, 0.01, want_centi=True)
+            s_i = i % 3
+            v = pipe.buffers(s_i, B, N)
+            assert v["guess_idx"].dtype == np.uint8 and v["guess_idx"].shape == (B, N, 3)
+            v["guess_idx"][:] = pack_idx24(idx)
+            v["guess_len"][:] = ln
+            v["answer_slot"][:] = slot
+            v["exact"][:] = ex
+            v["scores"][:] = -1.0
+            pipe.submit(s_i, 0.01, want_centi=True)
+            pipe.wait(s_i)
+            assert np.array_equal(v["scores"].view(np.uint32), want[0].view(np.uint32)), (route, B, N)
+            assert np.array_equal(v["centi"], want[1])
+    pipe.close()
+
+
 def test_overlapped_launches_match_serial(small_engine):
     """CM_SCORE_OVERLAP_PREVIOUS: back-to-back independent batches may overlap on the GPU;
     every batch must still come out bit-identical to a serial run, including right after
