@@ -625,14 +625,14 @@ def run_own(args) -> None:
         #     scores them, and the step's scores land back in page-locked host memory, where the
         #     host reads them.  The producer hands PIPE_PER_CALL steps to one cm_pipe_cycle_many call.
         # (b) synchronous: one cm_score_batch_host call per step (what Backend.compute_scores uses).
-        from cassmantle_b200.engine import ScoringPipe
+        from cassmantle_b200.engine import ScoringPipe, pack_idx24
 
-        def make_pipe():
-            pp = ScoringPipe(eng, depth=RING, max_guesses=B, max_slots=N)
+        def make_pipe(packed: bool = True):
+            pp = ScoringPipe(eng, depth=RING, max_guesses=B, max_slots=N, packed=packed)
             vv = []
             for s_i, (idx, ln, slot, ex) in enumerate(ring):
                 v = pp.buffers(s_i, B, N)
-                v["guess_idx"][:] = idx
+                v["guess_idx"][:] = ring_packed[s_i] if packed else idx
                 v["guess_len"][:] = ln
                 v["answer_slot"][:] = slot
                 v["exact"][:] = ex
@@ -640,7 +640,11 @@ def run_own(args) -> None:
             return pp, vv
 
         if pipe is None:
+            # word indices travel as 3 bytes each (cm_pipe_set_idx24; 3,000,000 rows < 2^24): a quarter fewer
+            # input bytes per step, which is what bounds several GPUs behind one host (pcie_ceiling below)
+            ring_packed = [pack_idx24(idx) for idx, _, _, _ in ring]
             pipe, views = make_pipe()
+            pipe_i32, views_i32 = make_pipe(packed=False)     # the same with 4-byte indices, for comparison
             # the same pipe pinned to each of its two routes, for comparison
             os.environ["CM_PIPE_ROUTE"] = "copy"          # H2D DMA -> kernel -> D2H DMA
             pipe_dma, views_dma = make_pipe()
@@ -667,7 +671,7 @@ def run_own(args) -> None:
                             wait(ph, (q - PIPE_DEPTH) % RING)
                             checksum += float(views[(q - PIPE_DEPTH) % RING]["scores"][0])
                         src, dst = h_np[(q + 1) % RING], views[q % RING]
-                        np.copyto(dst["guess_idx"], src[0]); np.copyto(dst["guess_len"], src[1])
+                        np.copyto(dst["guess_idx"], ring_packed[(q + 1) % RING]); np.copyto(dst["guess_len"], src[1])
                         np.copyto(dst["answer_slot"], src[2]); np.copyto(dst["exact"], src[3])
                         if submit(ph, q % RING, ms32, 0) != 0:
                             _lib.check(-1)
@@ -704,12 +708,13 @@ def run_own(args) -> None:
         run_pipe(args.warmup, args.steps)
         e2e_s = max_over_ranks(time.perf_counter() - t0)
         e2e_launches = int(lib.cm_kernel_launch_count() - launches1)
-        h2d = B * N * 4 + B * 4 + B * 4 + B
+        h2d = B * N * 3 + B * 4 + B * 4 + B
         e2e = {"value": args.steps * B * world / e2e_s, "unit": UNIT,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 4,
                "ms_per_step": e2e_s / args.steps * 1e3, "gpu_launches": e2e_launches, "warmup_steps": pipe_warmup,
-               "steps_per_call": PIPE_PER_CALL,
+               "steps_per_call": PIPE_PER_CALL, "index_bytes": 3,
                "api": f"cm_pipe_cycle_many (C ABI): {PIPE_PER_CALL} x (cm_pipe_wait + cm_pipe_submit) per call, "
+                      f"word indices as 3 bytes each (cm_pipe_set_idx24), "
                       f"{PIPE_DEPTH} batches in flight; each step's "
                       f"inputs cross PCIe from a page-locked host slot and its scores land back in it -- either read "
                       f"and written by the scoring kernel itself or moved by the copy engine, whichever the pipe "
@@ -729,6 +734,16 @@ def run_own(args) -> None:
         one_s = max_over_ranks(time.perf_counter() - t0)
         e2e["one_step_per_call"] = {"value": n_long_e * B * world / one_s, "unit": UNIT, "steps": n_long_e,
                                     "ms_per_step": one_s / n_long_e * 1e3, "api": "cm_pipe_cycle, one call per step"}
+        ph, all_views = pipe_i32._h, views_i32
+        run_pipe(0, pipe_warmup)
+        barrier()
+        t0 = time.perf_counter()
+        run_pipe(args.warmup, n_long_e)
+        i32_s = max_over_ranks(time.perf_counter() - t0)
+        e2e["int32_indices"] = {"value": n_long_e * B * world / i32_s, "unit": UNIT, "steps": n_long_e,
+                                "ms_per_step": i32_s / n_long_e * 1e3, "h2d_bytes_per_step": B * N * 4 + B * 9,
+                                "note": "the same pipe with 4-byte indices"}
+        ph, all_views = pipe._h, views
         # the ceiling of this figure: the same copies with no kernel at all, every rank at once -- what the
         # host and the PCIe path sustain (several GPUs share one host's memory system and PCIe switches)
         secs = ctypes.c_double(0.0)
@@ -740,6 +755,10 @@ def run_own(args) -> None:
                                "gbs_per_gpu": (h2d + B * 4) / (probe_s / n_probe) / 1e9,
                                "note": "H2D copy of a step's inputs + D2H copy of its scores per step through the "
                                        "copy engine, no kernel, all ranks at once (cm_pipe_probe_copies)"}
+        barrier()
+        _lib.check(lib.cm_pipe_probe_copies(pipe_i32._h, n_probe, PIPE_DEPTH, ctypes.byref(secs)))
+        probe32_s = max_over_ranks(secs.value)
+        e2e["pcie_ceiling"]["with_4_byte_indices"] = n_probe * B * world / probe32_s
         # (a'') the same call pinned to each route (the pipe itself times both as it runs and keeps
         #       the faster one: which one wins depends on how busy the PCIe path is)
         for tag, pp, vv, note in (("copy_engine_route", pipe_dma, views_dma, "CM_PIPE_ROUTE=copy: H2D DMA, kernel, D2H DMA per step"),
@@ -767,7 +786,7 @@ def run_own(args) -> None:
                                          "(rank-local figure)"}
         for s_i, (idx, ln, slot, ex) in enumerate(ring):        # restore the slots' own batches
             v = views[s_i]
-            v["guess_idx"][:] = idx; v["guess_len"][:] = ln; v["answer_slot"][:] = slot; v["exact"][:] = ex
+            v["guess_idx"][:] = ring_packed[s_i]; v["guess_len"][:] = ln; v["answer_slot"][:] = slot; v["exact"][:] = ex
         for i in range(args.warmup):
             step_host(i)
         torch.cuda.synchronize()
