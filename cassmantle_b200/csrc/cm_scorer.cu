@@ -188,6 +188,28 @@ __device__ __forceinline__ int32_t ld_idx(const int32_t *base, size_t k) {
     }
 }
 
+// Index c + sub of the guess whose first index is element g0, for every lane of an LPG-lane group
+// (-1 beyond n_slots).  IDX24 with n_slots a multiple of 4: the chunk's 3 * LPG bytes start on a word
+// boundary, so the group fetches them as LPG * 3 / 4 aligned words with ONE load instruction and every
+// lane cuts its three bytes out of two of them -- when the batch sits in page-locked host memory a
+// byte load is a PCIe request of its own.
+template <int LPG, bool IDX24>
+__device__ __forceinline__ int32_t ld_idx_chunk(const int32_t *base, size_t g0, int c, int n_slots, int sub, int grp_base) {
+    if constexpr (IDX24) {
+        if ((n_slots & 3) == 0) {                            // uniform over the launch
+            const uint32_t *w32 = reinterpret_cast<const uint32_t *>(reinterpret_cast<const uint8_t *>(base) + 3 * (g0 + c));
+            const int n_idx = min(LPG, n_slots - c);         // indices of this chunk (a multiple of 4)
+            const uint32_t word = sub < (3 * n_idx) / 4 ? w32[sub] : 0u;
+            const int w = (3 * sub) >> 2, sh = ((3 * sub) & 3) * 8;
+            const uint32_t lo = __shfl_sync(cm::kFullMask, word, grp_base + (w & (LPG - 1)));
+            const uint32_t hi = __shfl_sync(cm::kFullMask, word, grp_base + ((w + 1) & (LPG - 1)));
+            const uint32_t v = __funnelshift_r(lo, hi, sh) & 0xffffffu;
+            return (sub < n_idx && v != 0xffffffu) ? (int32_t)v : -1;
+        }
+    }
+    return (c + sub < n_slots) ? ld_idx<IDX24>(base, g0 + c + sub) : -1;
+}
+
 template <int VPL, int LPG, int R, bool STREAM, int THREADS, bool SINGLE, bool SYS = false, bool IDX24 = false>
 __device__ __forceinline__ void
 score_groups(int warp, const float *__restrict__ table, int64_t n_rows, int dim4,
@@ -229,7 +251,7 @@ score_groups(int warp, const float *__restrict__ table, int64_t n_rows, int dim4
         slot = answer_slot[b];
     }
     // SINGLE (n_slots == 1, the reference's own shape): every lane of the group reads the one index
-    int32_t mine = SINGLE ? ld_idx<IDX24>(guess_idx, g0) : ((sub < n_slots) ? ld_idx<IDX24>(guess_idx, g0 + sub) : -1);
+    int32_t mine = SINGLE ? ld_idx<IDX24>(guess_idx, g0) : ld_idx_chunk<LPG, IDX24>(guess_idx, g0, 0, n_slots, sub, grp_base);
     n = n < 0 ? 0 : (n > n_slots ? n_slots : n);
     const bool slot_ok = slot >= 0 && slot < n_answers;
 
@@ -278,7 +300,10 @@ score_groups(int warp, const float *__restrict__ table, int64_t n_rows, int dim4
         }
     } else
     for (int c = 0; c < n_max; c += LPG) {
-        if (c > 0) mine = (c + sub < n_live) ? ld_idx<IDX24>(guess_idx, g0 + c + sub) : 0;
+        if (c > 0) {                                         // every lane takes part (shuffles); dead slots become row 0, unused
+            mine = ld_idx_chunk<LPG, IDX24>(guess_idx, g0, c, n_slots, sub, grp_base);
+            if (c + sub >= n_live) mine = 0;
+        }
         const int m = min(LPG, n_max - c);
         for (int k = 0; k < m; k += R) {
             float4 buf[R][VPL];
@@ -778,6 +803,8 @@ int enqueue_score(cm_engine *e, const int32_t *guess_idx, const int32_t *guess_l
                   float *scores, int32_t *centi, uint32_t flags, cudaStream_t st, const ShipArgs *ship,
                   bool idx24) {
     if (int rc = check_engine(e)) return rc;
+    if (idx24 && ((uintptr_t)guess_idx & 3u))
+        return fail(CM_ERR_INVALID, "the block of 3-byte indices must start on a 4-byte boundary");
     if (idx24 && e->n_rows > 0xffffffLL)
         return fail(CM_ERR_INVALID, "3-byte indices need a table of at most 16,777,215 rows, this one has %lld",
                     (long long)e->n_rows);
