@@ -642,14 +642,17 @@ def run_own(args) -> None:
         if pipe is None:
             # word indices travel as 3 bytes each (cm_pipe_set_idx24; 3,000,000 rows < 2^24): a quarter fewer
             # input bytes per step, which is what bounds several GPUs behind one host (pcie_ceiling below)
+            # Rule: packed when several GPUs share the host (the PCIe path is the limit there), 4-byte indices on
+            # one GPU (the GPU is the limit; the kernel reads the slot in place).  Both are always measured.
             ring_packed = [pack_idx24(idx) for idx, _, _, _ in ring]
-            pipe, views = make_pipe()
-            pipe_i32, views_i32 = make_pipe(packed=False)     # the same with 4-byte indices, for comparison
+            use_packed = world > 1
+            pipe, views = make_pipe(packed=use_packed)
+            pipe_alt, views_alt = make_pipe(packed=not use_packed)     # the other index format, for comparison
             # the same pipe pinned to each of its two routes, for comparison
             os.environ["CM_PIPE_ROUTE"] = "copy"          # H2D DMA -> kernel -> D2H DMA
-            pipe_dma, views_dma = make_pipe()
+            pipe_dma, views_dma = make_pipe(packed=use_packed)
             os.environ["CM_PIPE_ROUTE"] = "inplace"       # the kernel reads/writes the pinned slot itself
-            pipe_inp, views_inp = make_pipe()
+            pipe_inp, views_inp = make_pipe(packed=use_packed)
             del os.environ["CM_PIPE_ROUTE"]
         submit, wait, cycle, many, ph = (lib.cm_pipe_submit, lib.cm_pipe_wait, lib.cm_pipe_cycle,
                                          lib.cm_pipe_cycle_many, pipe._h)
@@ -671,7 +674,7 @@ def run_own(args) -> None:
                             wait(ph, (q - PIPE_DEPTH) % RING)
                             checksum += float(views[(q - PIPE_DEPTH) % RING]["scores"][0])
                         src, dst = h_np[(q + 1) % RING], views[q % RING]
-                        np.copyto(dst["guess_idx"], ring_packed[(q + 1) % RING]); np.copyto(dst["guess_len"], src[1])
+                        np.copyto(dst["guess_idx"], ring_packed[(q + 1) % RING] if use_packed else src[0]); np.copyto(dst["guess_len"], src[1])
                         np.copyto(dst["answer_slot"], src[2]); np.copyto(dst["exact"], src[3])
                         if submit(ph, q % RING, ms32, 0) != 0:
                             _lib.check(-1)
@@ -708,14 +711,15 @@ def run_own(args) -> None:
         run_pipe(args.warmup, args.steps)
         e2e_s = max_over_ranks(time.perf_counter() - t0)
         e2e_launches = int(lib.cm_kernel_launch_count() - launches1)
-        h2d = B * N * 3 + B * 4 + B * 4 + B
+        h2d = B * N * (3 if use_packed else 4) + B * 4 + B * 4 + B
         e2e = {"value": args.steps * B * world / e2e_s, "unit": UNIT,
                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 4,
                "ms_per_step": e2e_s / args.steps * 1e3, "gpu_launches": e2e_launches, "warmup_steps": pipe_warmup,
-               "steps_per_call": PIPE_PER_CALL, "index_bytes": 3,
+               "steps_per_call": PIPE_PER_CALL, "index_bytes": 3 if use_packed else 4,
                "api": f"cm_pipe_cycle_many (C ABI): {PIPE_PER_CALL} x (cm_pipe_wait + cm_pipe_submit) per call, "
-                      f"word indices as 3 bytes each (cm_pipe_set_idx24), "
-                      f"{PIPE_DEPTH} batches in flight; each step's "
+                      + ("word indices as 3 bytes each (cm_pipe_set_idx24: several GPUs behind one host are bound by "
+                         "PCIe bytes), " if use_packed else "")
+                      + f"{PIPE_DEPTH} batches in flight; each step's "
                       f"inputs cross PCIe from a page-locked host slot and its scores land back in it -- either read "
                       f"and written by the scoring kernel itself or moved by the copy engine, whichever the pipe "
                       f"measures to be faster as it runs (both pinned routes are timed below); the timed region "
@@ -734,15 +738,23 @@ def run_own(args) -> None:
         one_s = max_over_ranks(time.perf_counter() - t0)
         e2e["one_step_per_call"] = {"value": n_long_e * B * world / one_s, "unit": UNIT, "steps": n_long_e,
                                     "ms_per_step": one_s / n_long_e * 1e3, "api": "cm_pipe_cycle, one call per step"}
-        ph, all_views = pipe_i32._h, views_i32
+        ph, all_views = pipe_alt._h, views_alt
+        barrier()
         run_pipe(0, pipe_warmup)
         barrier()
         t0 = time.perf_counter()
+        run_pipe(args.warmup, args.steps)
+        alt20_s = max_over_ranks(time.perf_counter() - t0)
+        barrier()
+        t0 = time.perf_counter()
         run_pipe(args.warmup, n_long_e)
-        i32_s = max_over_ranks(time.perf_counter() - t0)
-        e2e["int32_indices"] = {"value": n_long_e * B * world / i32_s, "unit": UNIT, "steps": n_long_e,
-                                "ms_per_step": i32_s / n_long_e * 1e3, "h2d_bytes_per_step": B * N * 4 + B * 9,
-                                "note": "the same pipe with 4-byte indices"}
+        alt_s = max_over_ranks(time.perf_counter() - t0)
+        alt_bytes = 4 if use_packed else 3
+        e2e["other_index_format"] = {"index_bytes": alt_bytes, "value": args.steps * B * world / alt20_s, "unit": UNIT,
+                                     "ms_per_step": alt20_s / args.steps * 1e3,
+                                     "sustained": {"value": n_long_e * B * world / alt_s, "steps": n_long_e},
+                                     "h2d_bytes_per_step": B * N * alt_bytes + B * 9,
+                                     "note": "the same pipe and the same K steps with the other index format"}
         ph, all_views = pipe._h, views
         # the ceiling of this figure: the same copies with no kernel at all, every rank at once -- what the
         # host and the PCIe path sustain (several GPUs share one host's memory system and PCIe switches)
@@ -756,9 +768,9 @@ def run_own(args) -> None:
                                "note": "H2D copy of a step's inputs + D2H copy of its scores per step through the "
                                        "copy engine, no kernel, all ranks at once (cm_pipe_probe_copies)"}
         barrier()
-        _lib.check(lib.cm_pipe_probe_copies(pipe_i32._h, n_probe, PIPE_DEPTH, ctypes.byref(secs)))
-        probe32_s = max_over_ranks(secs.value)
-        e2e["pcie_ceiling"]["with_4_byte_indices"] = n_probe * B * world / probe32_s
+        _lib.check(lib.cm_pipe_probe_copies(pipe_alt._h, n_probe, PIPE_DEPTH, ctypes.byref(secs)))
+        probe_alt_s = max_over_ranks(secs.value)
+        e2e["pcie_ceiling"]["with_the_other_index_format"] = n_probe * B * world / probe_alt_s
         # (a'') the same call pinned to each route (the pipe itself times both as it runs and keeps
         #       the faster one: which one wins depends on how busy the PCIe path is)
         for tag, pp, vv, note in (("copy_engine_route", pipe_dma, views_dma, "CM_PIPE_ROUTE=copy: H2D DMA, kernel, D2H DMA per step"),
@@ -786,7 +798,8 @@ def run_own(args) -> None:
                                          "(rank-local figure)"}
         for s_i, (idx, ln, slot, ex) in enumerate(ring):        # restore the slots' own batches
             v = views[s_i]
-            v["guess_idx"][:] = ring_packed[s_i]; v["guess_len"][:] = ln; v["answer_slot"][:] = slot; v["exact"][:] = ex
+            v["guess_idx"][:] = ring_packed[s_i] if use_packed else idx
+            v["guess_len"][:] = ln; v["answer_slot"][:] = slot; v["exact"][:] = ex
         for i in range(args.warmup):
             step_host(i)
         torch.cuda.synchronize()
