@@ -1,0 +1,65 @@
+"""Developer probe (torchrun, one rank per GPU): us per 4096x16 step with and without the fused score
+all-gather, for several ring depths (the peers are waited for with a lag of depth/2 steps)."""
+import ctypes, os, sys
+import numpy as np
+import torch
+import torch.distributed as dist
+sys.path.insert(0, ".")
+from cassmantle_b200 import _lib, synth
+from cassmantle_b200.dist import ScoreGather
+from cassmantle_b200.engine import ScoringEngine
+
+rank, local, world = int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+dist.init_process_group("nccl", device_id=dev)
+lib = _lib.load()
+V, B, N, RING = synth.FULL_ROWS, 4096, 16, 32
+eng = ScoringEngine.synthetic(V, 300, 0, local)
+ans = np.random.default_rng(999).choice(V, size=2, replace=False).astype(np.int32)
+eng.set_answers(ans); eng.synchronize()
+bufs = []
+for i in range(RING):
+    idx, ln, _, slot, ex = synth.make_guess_batch(B, N, V, 2, seed=1000 + 7919 * rank + i, near_frac=0.0)
+    bufs.append([torch.from_numpy(a).to(dev) for a in (idx, ln, slot, ex)])
+out = torch.empty(B, dtype=torch.float32, device=dev)
+stream = torch.cuda.Stream(device=dev); torch.cuda.set_stream(stream); st = stream.cuda_stream
+ms = ctypes.c_float(np.float32(0.01))
+
+def run(gather_h, flags, steps):
+    arr = (_lib.cm_batch * (2 * RING))()
+    for k in range(2 * RING):
+        q = bufs[k % RING]
+        arr[k] = _lib.cm_batch(q[0].data_ptr(), q[1].data_ptr(), q[2].data_ptr(), q[3].data_ptr(), out.data_ptr(), None, B, N)
+    def go(n):
+        i = 0
+        while i < n:
+            k = min(RING, n - i)
+            rc = lib.cm_score_batch_list_device(eng._h, gather_h, arr, k, ms, flags, st)
+            assert rc == 0, lib.cm_last_error()
+            i += k
+    go(200)
+    dist.barrier(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream); go(steps); e1.record(stream)
+    dist.barrier(); torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) * 1e3 / steps], dtype=torch.float64, device=dev)
+    allt = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(allt, t)
+    return [round(float(x.item()), 2) for x in allt]
+
+steps = 6000
+res = run(None, 1, steps)
+if rank == 0: print(f"world {world}: no gather: per rank {res} max {max(res)}", flush=True)
+for depth in (8, 16, 4):
+    for flags, tag in ((1, "wait lag depth/2"), (1 | _lib.CM_GATHER_DEFER_WAIT, "no peer wait in the ship")):
+        g = ScoreGather(eng, B, depth=depth)
+        g.exchange_handles()
+        dist.barrier()
+        res = run(g._h, flags, steps)
+        g.wait(st); torch.cuda.synchronize()
+        if rank == 0: print(f"world {world}: gather depth {depth}, {tag}: max {max(res)} us/step (timed out: {g.timed_out()})", flush=True)
+        dist.barrier()
+        g.close()
+eng.close()
+dist.destroy_process_group()
