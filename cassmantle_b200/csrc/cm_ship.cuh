@@ -84,42 +84,64 @@ __device__ __forceinline__ void ship_duty(const ShipArgs &a, int cta, int n_ctas
     }
     __syncthreads();
     if (tr) tr[2] = global_ns();
-    for (int i = lo + 4 * (int)threadIdx.x; i < hi; i += 4 * (int)blockDim.x) {
-        for (;;) {
-            uint4 v;
-            asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
-                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(a.stage + i) : "memory");
-            const bool pending = v.x == kShipSentinel || (i + 1 < hi && v.y == kShipSentinel) ||
-                                 (i + 2 < hi && v.z == kShipSentinel) || (i + 3 < hi && v.w == kShipSentinel);
-            if (!pending) {
+    // Up to kBatch 16-byte pieces per thread are asked for at once (independent loads: one L2 round trip,
+    // not kBatch of them -- the ship of one step used to spend 5.5 us here, and with two fences behind it
+    // took longer than the 11 us scoring step it rides in); a piece that still holds a sentinel is polled.
+    constexpr int kBatch = 8;
+    const int stride = 4 * (int)blockDim.x;
+    for (int base = lo + 4 * (int)threadIdx.x; base < hi; base += stride * kBatch) {
+        uint4 v[kBatch];
 #pragma unroll
-                for (int r = 0; r < kMaxPeers; ++r)
-                    if (r < a.world)
-                        *reinterpret_cast<uint4 *>(a.dst[r] + (size_t)a.rank * a.stride + i) = v;
-                if (a.copy_to != nullptr) {
-                    a.copy_to[i] = __uint_as_float(v.x);
-                    if (i + 1 < hi) a.copy_to[i + 1] = __uint_as_float(v.y);
-                    if (i + 2 < hi) a.copy_to[i + 2] = __uint_as_float(v.z);
-                    if (i + 3 < hi) a.copy_to[i + 3] = __uint_as_float(v.w);
+        for (int j = 0; j < kBatch; ++j) {
+            const int i = base + j * stride;
+            if (i < hi)
+                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(v[j].x), "=r"(v[j].y), "=r"(v[j].z), "=r"(v[j].w) : "l"(a.stage + i) : "memory");
+        }
+#pragma unroll
+        for (int j = 0; j < kBatch; ++j) {
+            const int i = base + j * stride;
+            if (i >= hi) continue;
+            for (;;) {
+                const bool pending = v[j].x == kShipSentinel || (i + 1 < hi && v[j].y == kShipSentinel) ||
+                                     (i + 2 < hi && v[j].z == kShipSentinel) || (i + 3 < hi && v[j].w == kShipSentinel);
+                if (!pending) break;
+                if (clock64() - t0 > a.timeout_cycles) {
+                    atomicExch(a.err, -(int)a.step);        // the scoring launch of that step never delivered
+                    break;
                 }
-                *reinterpret_cast<uint4 *>(a.stage + i) =
-                    make_uint4(kShipSentinel, kShipSentinel, kShipSentinel, kShipSentinel);
-                break;
+                __nanosleep(100);
+                asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(v[j].x), "=r"(v[j].y), "=r"(v[j].z), "=r"(v[j].w) : "l"(a.stage + i) : "memory");
             }
-            if (clock64() - t0 > a.timeout_cycles) {
-                atomicExch(a.err, -(int)a.step);        // the scoring launch of that step never delivered
-                break;
+#pragma unroll
+            for (int r = 0; r < kMaxPeers; ++r)
+                if (r < a.world)
+                    *reinterpret_cast<uint4 *>(a.dst[r] + (size_t)a.rank * a.stride + i) = v[j];
+            if (a.copy_to != nullptr) {
+                a.copy_to[i] = __uint_as_float(v[j].x);
+                if (i + 1 < hi) a.copy_to[i + 1] = __uint_as_float(v[j].y);
+                if (i + 2 < hi) a.copy_to[i + 2] = __uint_as_float(v[j].z);
+                if (i + 3 < hi) a.copy_to[i + 3] = __uint_as_float(v[j].w);
             }
-            __nanosleep(100);
+            *reinterpret_cast<uint4 *>(a.stage + i) =
+                make_uint4(kShipSentinel, kShipSentinel, kShipSentinel, kShipSentinel);
         }
     }
     if (tr) tr[3] = global_ns();
-    __threadfence_system();
+    // One system-scope fence, by the threads that publish, AFTER the barrier: fences are cumulative, so it
+    // covers every thread's peer stores that the barrier ordered before it.  (A fence per thread before the
+    // barrier and another before the flags cost 2.5-3.5 us each at 8 GPUs: measured, cm_gather_trace.)
     __syncthreads();
     if (tr) tr[4] = global_ns();
     if (threadIdx.x == 0) {
-        s_last = (n_ctas == 1) || (atomicAdd(a.counter, 1u) == (unsigned)n_ctas - 1u);
-        if (s_last && n_ctas > 1) *a.counter = 0u;
+        if (n_ctas == 1) {
+            s_last = 1;
+        } else {
+            __threadfence_system();                  // this CTA's stores, before the other CTAs may publish for it
+            s_last = atomicAdd(a.counter, 1u) == (unsigned)n_ctas - 1u;
+            if (s_last) *a.counter = 0u;
+        }
     }
     __syncthreads();
     // one thread per peer publishes: eight release stores from one thread cost ~2 us EACH

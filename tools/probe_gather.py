@@ -51,7 +51,7 @@ def run(gather_h, flags, steps):
 steps = 6000
 res = run(None, 1, steps)
 if rank == 0: print(f"world {world}: no gather: per rank {res} max {max(res)}", flush=True)
-for depth in (8, 16, 4):
+for depth in ((8,) if os.environ.get('CM_GATHER_TRACE') else (8, 16, 4)):
     for flags, tag in ((1, "wait lag depth/2"), (1 | _lib.CM_GATHER_DEFER_WAIT, "no peer wait in the ship")):
         g = ScoreGather(eng, B, depth=depth)
         g.exchange_handles()
@@ -59,6 +59,17 @@ for depth in (8, 16, 4):
         res = run(g._h, flags, steps)
         g.wait(st); torch.cuda.synchronize()
         if rank == 0: print(f"world {world}: gather depth {depth}, {tag}: max {max(res)} us/step (timed out: {g.timed_out()})", flush=True)
+        if rank == 0 and os.environ.get("CM_GATHER_TRACE") and flags == 1:
+            tr = np.zeros(512, dtype=np.uint64)
+            lib.cm_gather_trace(g._h, tr.ctypes.data)
+            tr = tr.reshape(64, 8); tr = tr[np.argsort(tr[:, 0])]
+            prev = None
+            for row in tr[-10:]:
+                b0 = int(row[1])
+                print("  ship of step", int(row[0]), "start +%.2f us after the previous ship's start;" % ((b0 - prev) / 1e3 if prev else 0.0),
+                      "own-order wait %.2f, staging+stores %.2f, fence %.2f, flags %.2f, peers %.2f us" % tuple(
+                          (int(row[i + 1]) - int(row[i])) / 1e3 for i in range(1, 6)), flush=True)
+                prev = b0
         dist.barrier()
         g.close()
 eng.close()
