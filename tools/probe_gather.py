@@ -48,6 +48,44 @@ def run(gather_h, flags, steps):
     dist.all_gather(allt, t)
     return [round(float(x.item()), 2) for x in allt]
 
+def regions(gather_h, flags, k, reps):
+    """`reps` timed regions of exactly k steps, each behind a barrier, an aligning all-reduce and an L2-flushing read."""
+    arr = (_lib.cm_batch * (2 * RING))()
+    for j in range(2 * RING):
+        q = bufs[j % RING]
+        arr[j] = _lib.cm_batch(q[0].data_ptr(), q[1].data_ptr(), q[2].data_ptr(), q[3].data_ptr(), out.data_ptr(), None, B, N)
+    flush = torch.zeros(512 << 20, dtype=torch.uint8, device=dev)
+    sink = torch.zeros((), dtype=torch.int64, device=dev)
+    al = torch.zeros(1, device=dev)
+    outl = []
+    for r in range(reps + 2):
+        dist.barrier(); torch.cuda.synchronize()
+        dist.all_reduce(al)
+        sink.copy_(torch.count_nonzero(flush))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        rc = lib.cm_score_batch_list_device(eng._h, gather_h, arr, k, ms, flags, st)
+        assert rc == 0
+        e1.record(stream)
+        dist.barrier(); torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) * 1e3 / k], dtype=torch.float64, device=dev)
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        if r >= 2:
+            outl.append([round(float(x.item()), 2) for x in allt])
+    return outl
+
+if os.environ.get("CM_PROBE_REGIONS"):
+    g = ScoreGather(eng, B, depth=8)
+    g.exchange_handles()
+    dist.barrier()
+    for row in regions(g._h, 1, 20, 10):
+        if rank == 0: print(f"world {world}: 20-step region, us/step per rank {row} max {max(row)}", flush=True)
+    g.wait(st); torch.cuda.synchronize(); dist.barrier(); g.close()
+    for row in regions(None, 1, 20, 4):
+        if rank == 0: print(f"world {world}: 20-step region, NO gather, us/step per rank {row} max {max(row)}", flush=True)
+    eng.close(); dist.destroy_process_group(); sys.exit(0)
+
 steps = 6000
 res = run(None, 1, steps)
 if rank == 0: print(f"world {world}: no gather: per rank {res} max {max(res)}", flush=True)
