@@ -432,14 +432,11 @@ def run_own(args) -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    flush_buf = torch.zeros(512 << 20, dtype=torch.uint8, device=dev)
-    flush_sink = torch.zeros((), dtype=torch.int64, device=dev)
     align_t = torch.zeros(1, dtype=torch.float32, device=dev)
-    # once now, so that the caching allocator holds the reduction's workspace and the communicator has
-    # seen this stream: a first-call cudaMalloc on one rank's host between the alignment and the timed
-    # launches is milliseconds that every other rank's ship CTA then waits for
+    # once now, so that the communicator has seen this stream: a first-call allocation on one rank's host
+    # between the alignment and the timed launches is milliseconds that every other rank's ship CTA waits for
     for _ in range(2):
-        flush_sink.copy_(torch.count_nonzero(flush_buf))
+        _lib.check(lib.cm_engine_flush_l2(eh, st))
         if world > 1:
             dist.all_reduce(align_t)
     torch.cuda.synchronize()
@@ -456,7 +453,7 @@ def run_own(args) -> None:
         # of device work and not the first launch's latency (K = 20 is a 0.25 ms region).
         if world > 1:
             dist.all_reduce(align_t)
-        flush_sink.copy_(torch.count_nonzero(flush_buf))     # a READ of 512 MB: L2 is left full of clean lines
+        _lib.check(lib.cm_engine_flush_l2(eh, st))            # a pure READ of 512 MB of the table: L2 is left full of clean lines
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         t_h = time.perf_counter()
@@ -1070,8 +1067,8 @@ def run_own(args) -> None:
                        "regions_ms": regions_ms, "region_reported": "median of three regions of exactly K steps",
                        "cpus_near_gpu": near_cpus,
                        "steps_enqueued_by": "cm_score_batch_list_device, one C-ABI call per <= 64 steps",
-                       "l2": f"ring of {RING} distinct batches over a 3.6 GB table (inputs >> L2); a 512 MB read "
-                             f"flushes L2 right before the first event of the timed region"},
+                       "l2": f"ring of {RING} distinct batches over a 3.6 GB table (inputs >> L2); a 512 MB read of "
+                             f"the table (cm_engine_flush_l2) flushes L2 right before the first event of the timed region"},
             "sustained": sustained,
             "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
             "cpu_baseline": cpu_baseline, "clocks": clocks, "latency": lat, "parity": parity,

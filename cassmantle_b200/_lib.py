@@ -43,6 +43,7 @@ _SIGNATURES = {
     "cm_engine_upload_rows": (_c.c_int, [_P, _P, _c.c_int64, _c.c_int64]),
     "cm_engine_download_rows": (_c.c_int, [_P, _P, _c.c_int64, _c.c_int64]),
     "cm_engine_fill_synthetic": (_c.c_int, [_P, _c.c_uint32]),
+    "cm_engine_flush_l2": (_c.c_int, [_P, _P]),
     "cm_engine_table": (_c.c_int, [_P, _c.POINTER(_P), _c.POINTER(_c.c_int64), _c.POINTER(_c.c_int)]),
     "cm_engine_stream": (_c.c_int, [_P, _c.POINTER(_P)]),
     "cm_engine_synchronize": (_c.c_int, [_P]),

@@ -132,6 +132,18 @@ __device__ __forceinline__ void group_unitvec(float4 (&m)[VPL]) {
     }
 }
 
+// Measurement aid (cm_engine_flush_l2): a pure READ of the first `n16` 16-byte pieces of the table, which
+// leaves L2 full of clean lines (a write flush leaves dirty ones for the next kernels to evict).
+__global__ void __launch_bounds__(256)
+cm_flush_read_kernel(const uint4 *__restrict__ p, size_t n16, unsigned *__restrict__ sink) {
+    unsigned acc = 0;
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n16; i += (size_t)gridDim.x * 256) {
+        const uint4 v = __ldcg(p + i);
+        acc ^= v.x ^ v.y ^ v.z ^ v.w;
+    }
+    if (acc == 0x5eed5eedu && sink != nullptr) *sink = acc;      // keeps the loads; practically never taken
+}
+
 // One warp per registered answer: ans_unit[a] = unitvec(table[answer_rows[a]]).
 template <int VPL>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
@@ -1013,6 +1025,17 @@ int cm_engine_fill_synthetic(cm_engine *e, uint32_t seed) {
     CM_CUDA(cudaGetLastError());
     CM_CUDA(cudaStreamSynchronize(e->stream));
     cm::similar_invalidate(e);
+    return CM_OK;
+}
+
+int cm_engine_flush_l2(cm_engine *e, void *stream) {
+    if (int rc = check_engine(e)) return rc;
+    DeviceGuard guard(e->device);
+    const size_t table_bytes = (size_t)e->n_rows * e->dim * sizeof(float);
+    const size_t bytes = table_bytes < ((size_t)512 << 20) ? table_bytes : ((size_t)512 << 20);
+    cm_flush_read_kernel<<<148 * 8, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<const uint4 *>(e->d_table),
+                                                                    bytes / 16, nullptr);
+    CM_CUDA(cudaGetLastError());
     return CM_OK;
 }
 

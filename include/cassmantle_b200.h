@@ -84,6 +84,10 @@ int cm_engine_table(cm_engine *e, void **d_table, int64_t *n_rows, int *dim);
 /* Copy table rows back to the host (tests: compare the synthetic fill with synth.py).    */
 int cm_engine_download_rows(cm_engine *e, float *rows, int64_t row0, int64_t n);
 
+/* Measurement aid: enqueue a pure read of the first 512 MB of the resident table on `stream`, which
+ * leaves the 126 MB L2 full of clean lines (benchmarks call it before a timed region).           */
+int cm_engine_flush_l2(cm_engine *e, void *stream);
+
 /* The engine's own stream as a cudaStream_t, and a blocking wait on it.                  */
 int cm_engine_stream(cm_engine *e, void **stream);
 int cm_engine_synchronize(cm_engine *e);
