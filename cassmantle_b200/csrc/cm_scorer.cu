@@ -533,166 +533,6 @@ cm_score1_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
     if (!waited) cm::pdl_wait();
 }
 
-// --------------------------------------------------------------------------------------
-// One-word guesses, one full wave or more: the rows travel through a per-warp ring of S stages in
-// shared memory, filled with 16-byte cp.async copies (LDGSTS) from every lane.  A stage is the four
-// rows of one group of guesses; S stages per warp are in flight while one is reduced from registers, and they cost
-// no registers, so the bytes in flight per SM no longer depend on how many warps sit in their load
-// phase (r2 capture of the register-staged kernel: 58 % long-scoreboard stalls, memory pipe part empty
-// while the warps convert and reduce).  Each warp owns a contiguous run of groups: one coalesced load
-// brings the metadata of 32 guesses (8 stages), the next 32 are fetched 8 stages ahead.
-// A lane copies exactly the 16-byte pieces it later reads (piece sub + 8 v of row grp), so waiting on
-// its own cp.async groups is all the synchronisation the ring needs.  Arithmetic and summation order
-// are those of cm_score_kernel<SINGLE> (group_unitvec<10, 8>, the same dot, group_sum<8>):
-// bit-identical scores.
-// --------------------------------------------------------------------------------------
-__device__ __forceinline__ void cp_async_row16(uint32_t smem_addr, const void *gmem) {
-    asm volatile("cp.async.cg.shared.global.L2::64B [%0], [%1], 16;" :: "r"(smem_addr), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
-
-template <int S, int THREADS, int MIN_BLOCKS, bool IDX24>
-__global__ void __launch_bounds__(THREADS, MIN_BLOCKS)
-cm_score1s_kernel(const float *__restrict__ table, int64_t n_rows, int dim4,
-                  const int32_t *__restrict__ guess_idx, const int32_t *__restrict__ guess_len,
-                  int n_guesses,
-                  const float *__restrict__ ans_unit, const int32_t *__restrict__ ans_rows,
-                  int n_answers, const int32_t *__restrict__ answer_slot,
-                  const uint8_t *__restrict__ exact, float min_score,
-                  float *__restrict__ scores, int32_t *__restrict__ centi, uint32_t flags,
-                  int n_ship_ctas, const cm::ShipArgs ship) {
-    constexpr int VPL = 10, LPG = 8, G = 4;
-    constexpr int kActive = 0, kExact = 1, kBad = 2, kNone = 3;
-    extern __shared__ __align__(16) unsigned char s_ring[];
-    if ((int)blockIdx.x < n_ship_ctas) {
-        cm::pdl_launch_dependents();
-        cm::ship_duty(ship, (int)blockIdx.x, n_ship_ctas);
-        return;
-    }
-    cm::pdl_launch_dependents();
-    const bool overlap = (flags & CM_SCORE_OVERLAP_PREVIOUS) != 0u;
-    if (!overlap) cm::pdl_wait();
-    bool waited = !overlap;
-    const int lane = threadIdx.x & 31;
-    const int sub = lane & (LPG - 1);
-    const int grp = lane / LPG;
-    const int warps_total = ((int)gridDim.x - n_ship_ctas) * (THREADS / 32);
-    const int w = ((int)blockIdx.x - n_ship_ctas) * (THREADS / 32) + (threadIdx.x >> 5);
-    const int n_groups = (n_guesses + G - 1) / G;
-    const int t_begin = (int)((int64_t)w * n_groups / warps_total);        // this warp's run of groups
-    const int t_count = (int)((int64_t)(w + 1) * n_groups / warps_total) - t_begin;
-    if (t_count <= 0) { if (!waited) cm::pdl_wait(); return; }
-    const int b_first = t_begin * G;
-    const float4 *table4 = reinterpret_cast<const float4 *>(table);
-    const int stage_f4 = G * dim4;
-    // this lane's corner of the ring: row grp of a stage, pieces sub, sub + 8, ...
-    float4 *ring = reinterpret_cast<float4 *>(s_ring) + (size_t)(threadIdx.x >> 5) * S * stage_f4 + grp * dim4 + sub;
-    const uint32_t ring_addr = (uint32_t)__cvta_generic_to_shared(ring);
-
-    // metadata of guess b_first + 32 c + lane of chunk c (8 stages), packed as row and slot << 2 | kind; three
-    // chunks are held -- current, next, and the one after, whose loads have 8 stages to complete
-    static_assert(S >= 1 && S <= 8, "a stage is issued at most one chunk ahead");
-    const int b_end = min(n_guesses, b_first + G * t_count);
-    auto load_meta = [&](int c, int32_t &row, int &meta) {
-        const int b = b_first + 32 * c + lane;
-        row = -1; meta = kNone;
-        if (b < b_end) {
-            const int32_t r = ld_idx<IDX24>(guess_idx, (size_t)b);
-            const int len = guess_len[b];
-            int slot = answer_slot[b];
-            const bool is_exact = exact != nullptr && exact[b] != 0;
-            const bool slot_ok = slot >= 0 && slot < n_answers;
-            const bool bad = len <= 0 || r < 0 || (int64_t)r >= n_rows || !slot_ok;
-            const int kind = is_exact ? kExact : (bad ? kBad : kActive);
-            if (kind == kActive) row = r;
-            meta = ((slot_ok ? slot : 0) << 2) | kind;
-        }
-    };
-    int32_t cur_row, nxt_row, far_row; int cur_meta, nxt_meta, far_meta;
-    load_meta(0, cur_row, cur_meta);
-    load_meta(1, nxt_row, nxt_meta);
-    load_meta(2, far_row, far_meta);
-    int chunk = 0;                                                        // chunk of cur_*
-
-    // stage u (a group of this warp's run): every lane asks for its pieces of row grp; always one commit
-#define CM_ISSUE_STAGE(U)                                                                              \
-    do {                                                                                               \
-        const int u_ = (U);                                                                            \
-        if (u_ < t_count) {                                                                            \
-            const int32_t pick_ = ((u_ >> 3) == chunk) ? cur_row : nxt_row;                            \
-            const int32_t r_ = __shfl_sync(cm::kFullMask, pick_, ((u_ & 7) << 2) + grp);               \
-            if (r_ >= 0) {                                                                             \
-                const float4 *src_ = table4 + (size_t)r_ * dim4 + sub;                                 \
-                const uint32_t dst_ = ring_addr + (uint32_t)((u_ % S) * stage_f4) * 16u;               \
-                _Pragma("unroll")                                                                      \
-                for (int v = 0; v < VPL; ++v)                                                          \
-                    if (sub + LPG * v < dim4) cp_async_row16(dst_ + (uint32_t)(LPG * v) * 16u, src_ + LPG * v); \
-            }                                                                                          \
-        }                                                                                              \
-        cp_async_commit();                                                                             \
-    } while (0)
-
-#pragma unroll
-    for (int u = 0; u < S; ++u) CM_ISSUE_STAGE(u);
-
-    for (int t = 0; t < t_count; ++t) {
-        if ((t >> 3) != chunk) {                                          // entering the next 32 guesses
-            chunk = t >> 3;
-            cur_row = nxt_row; cur_meta = nxt_meta;
-            nxt_row = far_row; nxt_meta = far_meta;
-            load_meta(chunk + 2, far_row, far_meta);
-        }
-        cp_async_wait<S - 1>();                                           // stage t has landed
-        const int owner = ((t & 7) << 2) + grp;
-        const int meta = __shfl_sync(cm::kFullMask, cur_meta, owner);
-        const int kind = meta & 3, slot = meta >> 2;
-        const int b = b_first + G * t + grp;
-        const bool active = kind == kActive;
-        float4 acc[VPL];
-        const float4 *stage = ring + (size_t)(t % S) * stage_f4;
-#pragma unroll
-        for (int v = 0; v < VPL; ++v) {
-            if (active && sub + LPG * v < dim4) acc[v] = stage[LPG * v];
-            else acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-        if (!waited) { cm::pdl_wait(); waited = true; }                   // answers / outputs: predecessor done
-        bool bad = kind == kBad;
-        if (active) {
-            const int32_t ar = ans_rows[slot];                            // unknown answer = KeyError too
-            bad = ar < 0 || (int64_t)ar >= n_rows;
-        }
-        // the stage is in registers once its squares are summed: its slot takes stage t + S, which is then
-        // in flight with the S - 1 behind it while this one is scaled and reduced
-        const double ss = lane_sumsq<VPL>(acc);
-        CM_ISSUE_STAGE(t + S);
-        float p = 0.f;
-        if (__any_sync(cm::kFullMask, active)) {
-            group_scale<VPL, LPG>(acc, ss);
-            const float4 *u4 = reinterpret_cast<const float4 *>(ans_unit) + (size_t)(active ? slot : 0) * dim4;
-            DotAcc dot;
-#pragma unroll
-            for (int v = 0; v < VPL; ++v) {
-                const int j = sub + LPG * v;
-                if (j < dim4) dot.add(acc[v], u4[j]);
-            }
-            p = group_sum<LPG>(dot.total());
-        }
-        float result;
-        if (kind == kExact) result = 1.0f;
-        else if (bad) result = min_score;
-        else result = (p > min_score) ? p : min_score;
-        if (kind != kNone && sub == 0) {
-            scores[b] = result;
-            if (centi != nullptr) centi[b] = (int32_t)floor((double)result * 10000.0 + 0.5);
-        }
-    }
-#undef CM_ISSUE_STAGE
-    cp_async_wait<0>();
-    if (!waited) cm::pdl_wait();
-}
-
 
 // --------------------------------------------------------------------------------------
 // Resident kernel for micro-batches (cm_engine_arm_resident).  One blocking host call for a few
@@ -849,7 +689,7 @@ namespace {
 //   persistent : the same with the next group's metadata prefetched -- very large one-word batches
 // Other table widths take the generic 32-lane kernel.  `CM_SCORE_KERNEL=wide|paired|single|persistent`
 // (environment, read once) overrides only the shape heuristic, for A/B timing of these four.
-enum ScoreKernel { kAuto = 0, kWide, kPaired, kSingle, kPersistent, kStaged };
+enum ScoreKernel { kAuto = 0, kWide, kPaired, kSingle, kPersistent };
 
 template <int VPL, int LPG, int R, bool STREAM, int THREADS, int MIN_BLOCKS, bool SINGLE = false, bool IDX24 = false>
 void launch_variant(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B, int N,
@@ -903,44 +743,6 @@ void launch_single_persistent(const cm_engine *e, const int32_t *gi, const int32
     cm::count_launch();
 }
 
-template <int S, int THREADS, int MIN_BLOCKS, bool IDX24>
-void launch_single_staged(const cm_engine *e, const int32_t *gi, const int32_t *gl, int B,
-                          const int32_t *slot, const uint8_t *exact, float min_score, float *scores,
-                          int32_t *centi, uint32_t flags, cudaStream_t st, const cm::ShipArgs *ship) {
-    constexpr int warps = THREADS / 32;
-    auto kernel = cm_score1s_kernel<S, THREADS, MIN_BLOCKS, IDX24>;
-    const size_t smem = (size_t)warps * S * 4 * (size_t)e->dim * sizeof(float);
-    static std::atomic<uint64_t> configured{0};                   // one bit per device
-    const uint64_t bit = 1ull << (e->device & 63);
-    if ((configured.load(std::memory_order_acquire) & bit) == 0) {
-        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-        configured.fetch_or(bit, std::memory_order_release);
-    }
-    const int n_groups = (B + 3) / 4;
-    const int needed = (n_groups + warps - 1) / warps;
-    const int resident = 148 * MIN_BLOCKS;
-    const int score_ctas = needed < resident ? needed : resident;
-    const bool shipping = ship != nullptr && ship->world > 0;
-    const int n_ship_ctas = shipping ? cm::ship_ctas(ship->n) : 0;
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)(score_ctas + n_ship_ctas));
-    cfg.blockDim = dim3(THREADS);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    cudaLaunchKernelEx(&cfg, kernel,
-                       (const float *)e->d_table, e->n_rows, e->dim / 4, gi, gl, B,
-                       (const float *)e->d_ans_unit, (const int32_t *)e->d_ans_rows, e->n_answers,
-                       slot, exact, min_score, scores, centi, flags, n_ship_ctas,
-                       shipping ? *ship : cm::ShipArgs{});
-    cm::count_launch();
-}
-
 ScoreKernel forced_kernel() {
     static const ScoreKernel v = [] {
         const char *s = getenv("CM_SCORE_KERNEL");
@@ -949,7 +751,6 @@ ScoreKernel forced_kernel() {
         if (strcmp(s, "paired") == 0) return kPaired;
         if (strcmp(s, "single") == 0) return kSingle;
         if (strcmp(s, "persistent") == 0) return kPersistent;
-        if (strcmp(s, "staged") == 0) return kStaged;
         return kAuto;
     }();
     return v;
@@ -967,30 +768,15 @@ void launch_score(const cm_engine *e, const int32_t *gi, const int32_t *gl, int 
         if (e->dim == 300) {
             // Measured on B200 (tools/probe_kernel.py, us per launch, CM_SCORE_OVERLAP_PREVIOUS):
             //   4096x16 : wide 12.9 | paired 11.6;  65536x16 200 | 181;  16384x8 30.4 | 24.1;  512x8 3.8 | 6.0
-            //   65536x1 : single 15.5 | persistent 15.9;  10^6 x1 : single 216 | persistent 191
+            //   65536x1 : single 15.2 | persistent 15.5;  131072x1 : 28.2 | 27.0;  262144x1 : 55.9 | 52.7;
+            //   10^6 x1 : 214 | 202
             ScoreKernel k = forced_kernel();
-            if ((k == kSingle || k == kPersistent || k == kStaged) && N != 1) k = kAuto;
+            if ((k == kSingle || k == kPersistent) && N != 1) k = kAuto;
             if (k == kAuto)
-                k = (N == 1) ? (B > (1 << 18) ? kPersistent : kSingle)
+                k = (N == 1) ? (B >= (1 << 17) ? kPersistent : kSingle)
                              : ((int64_t)B * N >= 32768 ? kPaired : kWide);
             if (IDX24 && k == kPersistent) k = kSingle;          // the persistent form takes 4-byte indices only
             switch (k) {
-                case kStaged: {
-#define CM_ST(S_, T_, M_) launch_single_staged<S_, T_, M_, IDX24>(e, gi, gl, B, slot, exact, min_score, scores, centi, flags, st, ship)
-                    static const int cfg_id = [] { const char *c = getenv("CM_STAGED_CFG"); return c ? atoi(c) : 0; }();
-                    switch (cfg_id) {
-                        case 1: CM_ST(1, 128, 6); break;
-                        case 2: CM_ST(2, 128, 5); break;
-                        case 3: CM_ST(2, 128, 4); break;
-                        case 4: CM_ST(3, 128, 3); break;
-                        case 5: CM_ST(1, 128, 10); break;
-                        case 6: CM_ST(1, 128, 7); break;
-                        case 7: CM_ST(2, 64, 9); break;
-                        default: CM_ST(1, 128, 8); break;
-                    }
-#undef CM_ST
-                    return;
-                }
                 case kPersistent:
                     if constexpr (!IDX24)
                         launch_single_persistent<10, 8, true, 128, 6>(e, gi, gl, B, slot, exact, min_score, scores, centi, flags, st, ship);
