@@ -73,6 +73,7 @@ _SIGNATURES = {
     "cm_vocab_lookup_host": (_c.c_int, [_P, _P, _P, _c.c_int, _P]),
     "cm_score_words_host": (_c.c_int, [_P, _P, _P, _P, _c.c_int, _P, _P, _c.c_int, _P, _c.c_float, _P, _P]),
     "cm_most_similar": (_c.c_int, [_P, _c.c_int32, _c.c_int, _P, _P, _c.POINTER(_c.c_int)]),
+    "cm_most_similar_batch": (_c.c_int, [_P, _P, _c.c_int, _c.c_int, _P, _P, _P]),
     "cm_semantic_distances": (_c.c_int, [_P, _P, _c.c_int, _c.c_int, _P]),
     "cm_blur_create": (_c.c_int, [_c.POINTER(_P), _c.c_int, _c.c_int, _c.c_int, _c.c_int, _c.c_int]),
     "cm_blur_destroy": (_c.c_int, [_P]),

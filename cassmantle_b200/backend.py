@@ -112,5 +112,20 @@ class Backend:
         result = [(keys[int(r)], float(s)) for r, s in zip(rows, sims) if int(r) != row]
         return result[:topn]
 
+    def most_similar_many(self, words, topn: int = 50) -> List[List[Tuple[str, float]]]:
+        """``[self.most_similar(w, topn) for w in words]`` with the table read once for all of them
+        (what a micro-batcher holding several such calls would issue)."""
+        rows = []
+        for word in words:
+            try:
+                rows.append(self.vocab.key_to_index[word.lower()])
+            except KeyError as e:
+                raise Exception("Word not in dictionary. ", e)
+        keys = self.vocab.index_to_key
+        out = []
+        for row, (got, sims) in zip(rows, self.engine.most_similar_batch(rows, topn + 1)):
+            out.append([(keys[int(r)], float(s)) for r, s in zip(got, sims) if int(r) != row][:topn])
+        return out
+
     def score_to_blur(self, score: float, min_blur: float = 0.0, max_blur: float = 15):
         return min_blur + (1 - score ** 2) * (max_blur - min_blur)    # backend.py:319-320

@@ -30,20 +30,16 @@
 
 #include "cm_common.cuh"
 #include "cm_internal.h"
+#include "cm_similar_state.h"
 
 namespace {
 
 using cm::fail;
 
-constexpr int kMaxTopK = 1024;
+constexpr int kMaxTopK = cm::kSimilarMaxTopK;
 constexpr int kRowsPerWarp = 4;
 
-// order-preserving map float -> uint32 (ascending); NaN -> 0 (smallest)
-__device__ __forceinline__ uint32_t key_of(float d) {
-    if (d != d) return 0u;
-    const uint32_t b = __float_as_uint(d);
-    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
-}
+__device__ __forceinline__ uint32_t key_of(float d) { return cm::similar_key_of(d); }
 
 __global__ void __launch_bounds__(256)
 cm_row_norm_kernel(const float *__restrict__ table, int64_t n_rows, int dim4, float *__restrict__ norms) {
@@ -468,22 +464,6 @@ cm_sort_kernel(const SelectState *st, const uint32_t *__restrict__ cand_key, con
 
 }  // namespace
 
-struct cm_similar_state {
-    float *d_norms = nullptr;
-    float *d_mean = nullptr;
-    float *d_dists = nullptr;
-    SelectState *d_sel = nullptr;
-    uint32_t *d_cand_key = nullptr;
-    int32_t *d_cand_row = nullptr;
-    int32_t *d_rows_out = nullptr;
-    float *d_sims_out = nullptr;
-    int *d_n_out = nullptr;
-    PickState *d_pick = nullptr;
-    unsigned char *h_result = nullptr;   // page-locked: rows[kMaxTopK] | sims[kMaxTopK] | n -- the kernels write it directly
-    unsigned long long *d_cand = nullptr;
-    bool norms_ready = false;
-};
-
 namespace cm {
 
 void similar_state_free(cm_engine *e) {
@@ -494,6 +474,7 @@ void similar_state_free(cm_engine *e) {
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (s->h_result) cudaFreeHost(s->h_result);
+    similar_batch_free(s);
     delete s;
     e->similar = nullptr;
 }
@@ -529,6 +510,26 @@ static int similar_state(cm_engine *e, cm_similar_state **out) {
     return CM_OK;
 }
 
+static bool generic_scan_forced() {
+    // Test hook: CM_SIMILAR_GENERIC_SCAN=1 forces the generic kernel so the two can be compared.
+    static const bool v = [] { const char *c = getenv("CM_SIMILAR_GENERIC_SCAN"); return c != nullptr && *c == '1'; }();
+    return v;
+}
+
+bool cm::similar_uses_scan16(int dim4) { return !generic_scan_forced() && dim4 > 64 && dim4 <= 80; }
+
+int cm::similar_prepare(cm_engine *e, cm_similar_state **out) {
+    cm_similar_state *s = nullptr;
+    if (int rc = similar_state(e, &s)) return rc;
+    if (!s->norms_ready) {                                           // gensim fill_norms(), once
+        cm_row_norm_kernel<<<148 * 8, 256, 0, e->stream>>>(e->d_table, e->n_rows, e->dim / 4, s->d_norms);
+        cm::count_launch();
+        s->norms_ready = true;
+    }
+    *out = s;
+    return CM_OK;
+}
+
 extern "C" int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_out, float *sims_out, int *n_out) {
     if (int rc = cm::check_engine(e)) return rc;
     if (row < 0 || (int64_t)row >= e->n_rows)
@@ -537,16 +538,14 @@ extern "C" int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_o
     if (!rows_out || !sims_out || !n_out) return fail(CM_ERR_INVALID, "an output pointer is NULL");
     std::lock_guard<std::mutex> lock(e->mu);
     cm::DeviceGuard guard(e->device);
+    return cm::most_similar_locked(e, row, k, rows_out, sims_out, n_out);
+}
+
+int cm::most_similar_locked(cm_engine *e, int32_t row, int k, int32_t *rows_out, float *sims_out, int *n_out) {
     cm_similar_state *s = nullptr;
-    if (int rc = similar_state(e, &s)) return rc;
+    if (int rc = cm::similar_prepare(e, &s)) return rc;
     cudaStream_t st = e->stream;
     const int dim4 = e->dim / 4;
-    const int grid = 148 * 8;                                        // row norms, once
-    if (!s->norms_ready) {                                           // gensim fill_norms(), once
-        cm_row_norm_kernel<<<grid, 256, 0, st>>>(e->d_table, e->n_rows, dim4, s->d_norms);
-        cm::count_launch();
-        s->norms_ready = true;
-    }
     const unsigned kk = (unsigned)((int64_t)k < e->n_rows ? k : e->n_rows);
     cm_query_kernel<<<1, 32, 0, st>>>(e->d_table, e->dim, row, s->d_norms, s->d_mean);
     cm::count_launch();
@@ -567,25 +566,23 @@ extern "C" int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_o
     }();
     const float *table = e->d_table, *mean = s->d_mean, *norms = s->d_norms;
     // 300-d tables (65..80 float4 per row) take the 16-lane scan: 580 against 594 us per query at
-    // 3M rows, A/B on one box, two runs each (profiles/r2_similar_ab.txt).  Test hook:
-    // CM_SIMILAR_GENERIC_SCAN=1 forces the generic kernel so the two can be compared.
-    static const bool generic_scan = [] { const char *v = getenv("CM_SIMILAR_GENERIC_SCAN"); return v != nullptr && *v == '1'; }();
-    if (!generic_scan && dim4 > 64 && dim4 <= 80) {
+    // 3M rows, A/B on one box, two runs each (profiles/r2_similar_ab.txt).
+    if (cm::similar_uses_scan16(dim4)) {
         cfg.blockDim = dim3(128);
         cfg.gridDim = dim3((unsigned)((e->n_rows + 127) / 128));
-        cudaLaunchKernelEx(&cfg, cm_scan16_kernel<5>, table, e->n_rows, dim4, mean, norms, s->d_dists, s->d_pick);
+        cudaLaunchKernelEx(&cfg, cm_scan16_kernel<5>, table, e->n_rows, dim4, mean, norms, s->d_dists, (PickState *)s->d_pick);
     } else {
     cfg.blockDim = dim3(256);
 #define CM_CASE(V, MB)                                                                             \
     case V:                                                                                        \
         cfg.gridDim = dim3(148 * MB);                                                              \
-        cudaLaunchKernelEx(&cfg, cm_scan_kernel<V, MB>, table, e->n_rows, dim4, mean, norms, s->d_dists, s->d_pick); \
+        cudaLaunchKernelEx(&cfg, cm_scan_kernel<V, MB>, table, e->n_rows, dim4, mean, norms, s->d_dists, (PickState *)s->d_pick); \
         break;
     switch ((dim4 + 31) / 32) {
         CM_CASE(1, 3) CM_CASE(2, 3) CM_CASE(3, 3) CM_CASE(4, 2) CM_CASE(5, 2) CM_CASE(6, 2) CM_CASE(7, 2)
         default:
             cfg.gridDim = dim3(148 * 2);
-            cudaLaunchKernelEx(&cfg, cm_scan_kernel<8, 2>, table, e->n_rows, dim4, mean, norms, s->d_dists, s->d_pick);
+            cudaLaunchKernelEx(&cfg, cm_scan_kernel<8, 2>, table, e->n_rows, dim4, mean, norms, s->d_dists, (PickState *)s->d_pick);
             break;
     }
 #undef CM_CASE
@@ -597,7 +594,7 @@ extern "C" int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_o
     int32_t *h_rows = reinterpret_cast<int32_t *>(s->h_result);
     float *h_sims = reinterpret_cast<float *>(s->h_result + kMaxTopK * 4);
     int *h_n = reinterpret_cast<int *>(s->h_result + kMaxTopK * 8);
-    cudaLaunchKernelEx(&cfg, cm_pick_kernel, (const float *)s->d_dists, e->n_rows, s->d_pick,
+    cudaLaunchKernelEx(&cfg, cm_pick_kernel, (const float *)s->d_dists, e->n_rows, (PickState *)s->d_pick,
                        kk, bucket_cap, s->d_cand, h_rows, h_sims, h_n);
     cm::count_launch();
     CM_CUDA(cudaGetLastError());
@@ -612,12 +609,12 @@ extern "C" int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_o
     // radix select over the distances the scan left behind.
     CM_CUDA(cudaMemsetAsync(s->d_sel, 0, sizeof(SelectState), st));
     for (int pass = 0; pass < 4; ++pass) {
-        cm_hist_kernel<<<148 * 4, 256, 0, st>>>(s->d_dists, e->n_rows, s->d_sel, pass, kk);
+        cm_hist_kernel<<<148 * 4, 256, 0, st>>>(s->d_dists, e->n_rows, (SelectState *)s->d_sel, pass, kk);
         cm::count_launch();
     }
-    cm_collect_kernel<<<148 * 4, 256, 0, st>>>(s->d_dists, e->n_rows, s->d_sel, kk, s->d_cand_key, s->d_cand_row);
+    cm_collect_kernel<<<148 * 4, 256, 0, st>>>(s->d_dists, e->n_rows, (SelectState *)s->d_sel, kk, s->d_cand_key, s->d_cand_row);
     cm::count_launch();
-    cm_sort_kernel<<<1, 1024, 0, st>>>(s->d_sel, s->d_cand_key, s->d_cand_row, s->d_dists, kk, s->d_rows_out,
+    cm_sort_kernel<<<1, 1024, 0, st>>>((const SelectState *)s->d_sel, s->d_cand_key, s->d_cand_row, s->d_dists, kk, s->d_rows_out,
                                        s->d_sims_out, s->d_n_out);
     cm::count_launch();
     CM_CUDA(cudaGetLastError());
@@ -631,6 +628,6 @@ extern "C" int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_o
 // The table changed (upload / synthetic fill): the cached row norms are stale.
 namespace cm {
 void similar_invalidate(cm_engine *e) {
-    if (e->similar) e->similar->norms_ready = false;
+    if (e->similar) { e->similar->norms_ready = false; e->similar->batch_table_stale = true; }
 }
 }  // namespace cm

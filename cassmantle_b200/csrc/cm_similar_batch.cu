@@ -1,0 +1,768 @@
+// cassmantle_b200 -- most_similar for a BATCH of query words in one pass over the table
+// (include/...: cm_most_similar_batch).
+//
+// Reference: Backend.most_similar, src/backend.py:297-301, called once per word; the micro-batcher
+// (cassmantle_b200/server.py) can hold many such calls.  One query is a 3M x 300 mat-vec bound by the
+// 3.6 GB table read (cm_similar.cu, 580 us).  Q queries are  [3M x 300] . [300 x Q]  -- the one
+// GEMM-shaped piece of work on this path -- and the table is read once for all of them:
+//
+//   cm_query_batch_kernel  mean[q] = unitvec(vectors[w_q] / norms[w_q])              (as cm_query_kernel)
+//   cm_simscan_tc_kernel   tcgen05.mma kind::tf32, M = 128 table rows per tile, N = Q (padded to 16),
+//                          K = 300 in ten 128-byte chunks fed by TMA (SWIZZLE_128B, out-of-range columns
+//                          zero-filled), fp32 accumulators in tensor memory, double-buffered so the epilogue
+//                          of one tile overlaps the MMAs of the next.  One persistent CTA per SM:
+//                          warp 0 = TMA producer, warp 1 = MMA issuer, warps 2-9 = epilogue.
+//                          The tf32 cosines are only a FILTER (|error| < 2^-9, see kBand):
+//                            mode 0  sample pass over every S-th tile: approximate cosines written out,
+//                                    cm_kth_kernel takes the k-th largest per query as threshold tau_q
+//                            mode 1  full pass: every (row, q) with cosine >= tau_q - band is a candidate
+//   cm_rescore_kernel      candidates re-scored in fp32 with exactly the arithmetic of the one-query scan
+//                          (same lanes, same FMA order, dot / norm)
+//   cm_topk_kernel         per query: sorted (cosine desc, row asc), top k out.
+// The k-th largest of a sample is a lower bound of the k-th largest overall, and the band covers the tf32
+// error on both sides, so every true top-k row is among the candidates: rows and cosines are those of Q
+// calls of cm_most_similar, bit for bit (ties at the k-th place may resolve differently, as they may there).
+// A query with more candidates than kCandCap (or fewer than k) is finished by the one-query path.
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+#include "cm_common.cuh"
+#include "cm_internal.h"
+#include "cm_similar_state.h"
+
+namespace {
+
+using cm::fail;
+
+constexpr int kTileRows = 128;          // UMMA M
+constexpr int kChunkFloats = 32;        // one 128-byte swizzle row of K
+constexpr int kMaxChunks = 10;          // dim <= 320
+constexpr int kMaxStages = 8;           // A ring: up to 8 x 16 KB (what the query block leaves free)
+constexpr int kStageBytes = kTileRows * kChunkFloats * 4;
+constexpr int kMaxNQ = 128;             // queries per pass (UMMA N)
+constexpr int kTmemCols = 256;          // two accumulators of kMaxNQ columns
+constexpr int kScanThreads = 320;        // TMA warp, MMA warp, eight epilogue warps
+constexpr unsigned kCandCap = 8192;     // candidates per query the re-score kernel sorts in shared memory
+// tf32 keeps 10 mantissa bits (truncation): each product is off by < 2^-9 relative, so a cosine (unit query,
+// division by the row norm) by < 2^-9 absolute.  Threshold and candidate are both approximate: 2 x 2^-9.
+constexpr float kBand = 4.0e-3f;
+constexpr unsigned long long kWaitCycles = 4000000000ull;   // ~2 s: a wait that long is a bug, trap instead of hanging
+
+// ---- PTX wrappers -------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                 "selp.b32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+// Bounded: records `code` and traps when the barrier does not flip within kWaitCycles.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity, unsigned *err, unsigned code) {
+    if (mbar_try_wait(bar, parity)) return;
+    const unsigned long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity)) {
+        if (clock64() - t0 > kWaitCycles) {
+            atomicExch(err, code);
+            __threadfence_system();
+            __trap();
+        }
+    }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 :: "r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" :: "r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem] . B[smem]^T, tf32 inputs, fp32 accumulate (ACC = false overwrites D)
+template <bool ACC>
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc) {
+    asm volatile("{\n\t.reg .pred p;\n\t"
+                 "setp.ne.b32 p, %4, 0;\n\t"
+                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 :: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "n"(ACC ? 1 : 0) : "memory");
+}
+// 16 consecutive fp32 columns of this thread's TMEM lane
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, float (&v)[16]) {
+    uint32_t r[16];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                   "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major operand tile in the SWIZZLE_128B layout TMA writes: rows of 128 bytes, 8-row groups 1024 bytes apart.
+// (cute::UMMA::SmemDescriptor: start >> 4 | LBO 1 << 16 | SBO 64 << 32 | version 1 << 46 | SWIZZLE_128B 2 << 61)
+__device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t smem_addr) {
+    const uint32_t lo = ((smem_addr >> 4) & 0x3fffu) | (1u << 16);
+    const uint32_t hi = 64u | (1u << 14) | (2u << 29);
+    return ((uint64_t)hi << 32) | lo;
+}
+
+enum : unsigned { kErrNone = 0, kErrEmpty = 1, kErrFull = 2, kErrQueries = 3, kErrTmemEmpty = 4, kErrTmemFull = 5 };
+
+struct ScanArgs {
+    const float *norms;
+    int64_t n_rows;
+    int n_visits;            // tiles this launch visits: tile = tile_first + visit * tile_stride
+    int tile_stride;
+    int nq;                  // UMMA N: queries padded to a multiple of 16, <= kMaxNQ
+    int dim;
+    int mode;                // 0 = sample (write cosines), 1 = filter (collect candidates)
+    int stages;              // A-ring depth (2 .. kMaxStages): what fits beside the query block
+    float *sample_out;       // [nq][sample_ld]
+    int64_t sample_ld;
+    const float *tau;        // [nq] thresholds, band already subtracted
+    int32_t *cand;           // [nq][kCandCap]
+    unsigned *cnt;           // [nq]
+    unsigned *err;
+};
+
+// --------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kScanThreads, 1)
+cm_simscan_tc_kernel(const __grid_constant__ CUtensorMap map_table, const __grid_constant__ CUtensorMap map_queries,
+                     const ScanArgs a) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    // carve: [A ring][queries: n_chunks x nq x 128 B][tau][barriers][tmem ptr]
+    unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const int n_chunks = (a.dim + kChunkFloats - 1) / kChunkFloats;
+    const uint32_t q_chunk_bytes = (uint32_t)a.nq * 128u;
+    unsigned char *s_a = smem;
+    unsigned char *s_q = s_a + a.stages * kStageBytes;
+    float *s_tau = reinterpret_cast<float *>(s_q + (size_t)n_chunks * q_chunk_bytes);
+    uint64_t *bars = reinterpret_cast<uint64_t *>(s_tau + kMaxNQ);
+    uint64_t *bar_full = bars, *bar_empty = bars + kMaxStages, *bar_q = bars + 2 * kMaxStages;
+    uint64_t *bar_tfull = bars + 2 * kMaxStages + 1, *bar_tempty = bars + 2 * kMaxStages + 3;
+    uint32_t *s_tmem = reinterpret_cast<uint32_t *>(bars + 2 * kMaxStages + 5);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int my_visits = a.n_visits > (int)blockIdx.x ? (a.n_visits - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < kMaxStages; ++i) { mbar_init(smem_u32(bar_full + i), 1); mbar_init(smem_u32(bar_empty + i), 1); }
+        mbar_init(smem_u32(bar_q), 1);
+        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(bar_tfull + i), 1); mbar_init(smem_u32(bar_tempty + i), 8); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {                                      // one warp allocates tensor memory (and frees it at the end)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(s_tmem)), "r"((uint32_t)kTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    if (threadIdx.x < kMaxNQ) s_tau[threadIdx.x] = (a.mode == 1 && (int)threadIdx.x < a.nq) ? a.tau[threadIdx.x] : 0.f;
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *s_tmem;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0 && my_visits > 0) {
+            mbar_expect_tx(smem_u32(bar_q), (uint32_t)n_chunks * q_chunk_bytes);
+            for (int c = 0; c < n_chunks; ++c)
+                tma_load_2d(smem_u32(s_q) + (uint32_t)c * q_chunk_bytes, &map_queries, c * kChunkFloats, 0, smem_u32(bar_q));
+            uint32_t s = 0, ph = 0;
+            for (int v = 0; v < my_visits; ++v) {
+                const int tile = ((int)blockIdx.x + v * (int)gridDim.x) * a.tile_stride;
+                for (int c = 0; c < n_chunks; ++c) {
+                    mbar_wait(smem_u32(bar_empty + s), ph ^ 1u, a.err, kErrEmpty);
+                    mbar_expect_tx(smem_u32(bar_full + s), kStageBytes);
+                    tma_load_2d(smem_u32(s_a) + s * kStageBytes, &map_table, c * kChunkFloats, tile * kTileRows, smem_u32(bar_full + s));
+                    if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1u; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0 && my_visits > 0) {
+            // instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, tf32 x tf32, both K-major, N, M = 128
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(a.nq >> 3) << 17) | ((uint32_t)(kTileRows >> 4) << 24);
+            mbar_wait(smem_u32(bar_q), 0, a.err, kErrQueries);
+            // The issuing thread is the serial resource of this kernel (one instruction per 8 columns of K): descriptors
+            // are running sums, the ring position a counter, the four MMAs of a chunk straight-line code.
+            const uint64_t da0 = umma_desc_k_sw128(smem_u32(s_a));
+            const uint64_t db0 = umma_desc_k_sw128(smem_u32(s_q));
+            const uint64_t db_step = q_chunk_bytes >> 4, da_step = kStageBytes >> 4;
+            const int last_steps = (a.dim - (n_chunks - 1) * kChunkFloats + 7) / 8;           // tf32: K = 8 per instruction
+            uint32_t s = 0, ph = 0;
+            uint64_t da = da0;
+            for (int v = 0; v < my_visits; ++v) {
+                const uint32_t acc = (uint32_t)v & 1u, tph = ((uint32_t)v >> 1) & 1u;
+                mbar_wait(smem_u32(bar_tempty + acc), tph ^ 1u, a.err, kErrTmemEmpty);     // epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * (uint32_t)a.nq;
+                uint64_t db = db0;
+                for (int c = 0; c < n_chunks; ++c) {
+                    mbar_wait(smem_u32(bar_full + s), ph, a.err, kErrFull);
+                    tc_fence_after();
+                    if (c == 0) tc_mma_tf32<false>(d_tmem, da, db, idesc);                    // +32 bytes of K = +2 in the address field
+                    else tc_mma_tf32<true>(d_tmem, da, db, idesc);
+                    if (c + 1 < n_chunks || last_steps == 4) {
+                        tc_mma_tf32<true>(d_tmem, da + 2, db + 2, idesc);
+                        tc_mma_tf32<true>(d_tmem, da + 4, db + 4, idesc);
+                        tc_mma_tf32<true>(d_tmem, da + 6, db + 6, idesc);
+                    } else {
+                        for (int k = 1; k < last_steps; ++k) tc_mma_tf32<true>(d_tmem, da + 2 * k, db + 2 * k, idesc);
+                    }
+                    tc_commit(smem_u32(bar_empty + s));                                       // stage free once these MMAs have read it
+                    db += db_step;
+                    da += da_step;
+                    if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1u; da = da0; }
+                }
+                tc_commit(smem_u32(bar_tfull + acc));                                         // accumulator complete
+            }
+        }
+    } else {
+        // ===== epilogue: warps 2..9.  A warp may only read TMEM lanes 32 * (warp % 4) .. + 32 (= tile rows); the two
+        // warps of a quarter split the query columns in blocks of 16 =====
+        const int quarter = warp & 3;
+        const int half = (warp - 2) >> 2;
+        const int row_in_tile = quarter * 32 + lane;
+        // this row's norm, fetched two tiles ahead: under the scan's own traffic a load takes about as long as a tile
+        auto norm_of = [&](int v) -> float {
+            if (v >= my_visits) return 1.f;
+            const int64_t r = (int64_t)((int)blockIdx.x + v * (int)gridDim.x) * a.tile_stride * kTileRows + row_in_tile;
+            return r < a.n_rows ? a.norms[r] : __int_as_float(0x7fc00000);          // rows past the end: NaN, never a candidate
+        };
+        float nrm0 = norm_of(0), nrm1 = norm_of(1);
+        for (int v = 0; v < my_visits; ++v) {
+            const int visit = (int)blockIdx.x + v * (int)gridDim.x;
+            const int tile = visit * a.tile_stride;
+            const uint32_t acc = (uint32_t)v & 1u, tph = ((uint32_t)v >> 1) & 1u;
+            const int64_t row = (int64_t)tile * kTileRows + row_in_tile;
+            const float nrm2 = norm_of(v + 2);
+            const float inv = 1.0f / nrm0;
+            nrm0 = nrm1;
+            nrm1 = nrm2;
+            mbar_wait(smem_u32(bar_tfull + acc), tph, a.err, kErrTmemFull);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * (uint32_t)a.nq;
+            for (int c0 = 16 * half; c0 < a.nq; c0 += 32) {
+                float d[16];
+                __syncwarp();                                    // tcgen05.ld is warp-wide: rejoin after the emit branch
+                tc_ld16(taddr + (uint32_t)c0, d);
+                if (a.mode == 0) {
+                    float *out = a.sample_out + (int64_t)c0 * a.sample_ld + (int64_t)visit * kTileRows + row_in_tile;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) out[(int64_t)i * a.sample_ld] = d[i] * inv;
+                } else {
+                    // straight-line compare of 16 cosines against their thresholds (broadcast reads), one rarely taken branch
+                    const float4 *t4 = reinterpret_cast<const float4 *>(s_tau + c0);
+                    unsigned hits = 0;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float4 t = t4[i];
+                        d[4 * i + 0] *= inv; d[4 * i + 1] *= inv; d[4 * i + 2] *= inv; d[4 * i + 3] *= inv;
+                        hits |= (d[4 * i + 0] >= t.x ? 1u : 0u) << (4 * i);
+                        hits |= (d[4 * i + 1] >= t.y ? 1u : 0u) << (4 * i + 1);
+                        hits |= (d[4 * i + 2] >= t.z ? 1u : 0u) << (4 * i + 2);
+                        hits |= (d[4 * i + 3] >= t.w ? 1u : 0u) << (4 * i + 3);
+                    }
+                    while (hits != 0u) {
+                        const int i = __ffs(hits) - 1;
+                        hits &= hits - 1u;
+                        const unsigned slot = atomicAdd(a.cnt + c0 + i, 1u);
+                        if (slot < kCandCap) a.cand[(size_t)(c0 + i) * kCandCap + slot] = (int32_t)row;
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(bar_tempty + acc));
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"((uint32_t)kTmemCols) : "memory");
+    }
+}
+
+
+// mean[q] = unitvec(vectors[w_q] / norms[w_q]) -- one warp per query, the arithmetic of cm_query_kernel; rows of
+// `mean` past n_queries (padding up to the UMMA N) are zeroed.
+__global__ void cm_query_batch_kernel(const float *__restrict__ table, int dim, const int32_t *__restrict__ rows,
+                                      int n_queries, const float *__restrict__ norms, float *__restrict__ mean) {
+    const int lane = threadIdx.x, q = blockIdx.x;
+    float *m = mean + (size_t)q * dim;
+    if (q >= n_queries) {
+        for (int j = lane; j < dim; j += 32) m[j] = 0.f;
+        return;
+    }
+    const int32_t row = rows[q];
+    const float nrm = norms[row];
+    double ss = 0.0;
+    for (int j = lane; j < dim; j += 32) {
+        const float x = table[(size_t)row * dim + j] / nrm;          // get_vector(key, norm=True)
+        m[j] = x;
+        ss = fma((double)x, (double)x, ss);
+    }
+    ss = cm::warp_sum(ss);
+    __syncwarp();
+    if (ss > 0.0) {                                                  // matutils.unitvec
+        const double inv = 1.0 / sqrt(ss);
+        for (int j = lane; j < dim; j += 32) m[j] = (float)((double)m[j] * inv);
+    }
+}
+
+// experiment: rows re-pitched to `pitch4` float4 (a multiple of 128 bytes), zero-filled past dim4
+__global__ void __launch_bounds__(256)
+cm_pad_rows_kernel(const float4 *__restrict__ table, int64_t n_rows, int dim4, int pitch4, float4 *__restrict__ out) {
+    const int64_t total = n_rows * pitch4;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
+        const int64_t r = i / pitch4;
+        const int j = (int)(i % pitch4);
+        out[i] = j < dim4 ? table[r * dim4 + j] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+
+__device__ __forceinline__ float float_of_key(uint32_t key) {        // inverse of similar_key_of (NaN was 0)
+    if (key == 0u) return __int_as_float(0x7fc00000);
+    return __uint_as_float((key & 0x80000000u) ? (key & 0x7fffffffu) : ~key);
+}
+
+// tau[q] = (k-th largest of the n sampled cosines of query q) - band; one CTA per query, 4-pass radix select.
+__global__ void __launch_bounds__(1024)
+cm_kth_kernel(const float *__restrict__ sample, int64_t ld, int64_t n, unsigned k, float band, float *__restrict__ tau, int n_real) {
+    __shared__ unsigned hist[256 * 32];                               // [bin][lane]: a warp's 32 adds never share a bank
+    __shared__ uint32_t s_prefix;
+    __shared__ unsigned s_rem;
+    const float *d = sample + (int64_t)blockIdx.x * ld;
+    if ((int)blockIdx.x >= n_real) {                                  // padding up to the UMMA N: nothing is a candidate
+        if (threadIdx.x == 0) tau[blockIdx.x] = __int_as_float(0x7f800000);
+        return;
+    }
+    if (threadIdx.x == 0) { s_prefix = 0u; s_rem = k; }
+    for (int pass = 0; pass < 4; ++pass) {
+        for (int i = threadIdx.x; i < 256 * 32; i += blockDim.x) hist[i] = 0u;
+        __syncthreads();
+        const uint32_t prefix = s_prefix;
+        const uint32_t mask = pass == 0 ? 0u : (0xffffffffu << (32 - 8 * pass));
+        const int shift = 24 - 8 * pass;
+        for (int64_t i0 = threadIdx.x; i0 < n; i0 += 8 * (int64_t)blockDim.x) {     // eight loads in flight per thread
+            float x[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int64_t i = i0 + u * (int64_t)blockDim.x;
+                x[u] = i < n ? __ldcg(d + i) : __int_as_float(0x7fc00000);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const uint32_t key = cm::similar_key_of(x[u]);
+                if (i0 + u * (int64_t)blockDim.x < n && (key & mask) == prefix)
+                    atomicAdd(&hist[((key >> shift) & 0xffu) * 32 + (threadIdx.x & 31)], 1u);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < 256) {                                      // fold the 32 copies into copy 0
+            unsigned sum = 0;
+            for (int l = 0; l < 32; ++l) sum += hist[threadIdx.x * 32 + ((l + threadIdx.x) & 31)];
+            __syncwarp();
+            hist[threadIdx.x * 32] = sum;
+        }
+        __syncthreads();
+        if (threadIdx.x < 32) {                                       // which bin, from the top, holds the rem-th entry
+            const int lane = threadIdx.x;
+            const int first = 255 - 8 * lane;                         // this lane's bins: first, first - 1, ..., first - 7
+            const unsigned rem = s_rem;
+            unsigned cnt8[8], mine = 0;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { cnt8[i] = hist[(first - i) * 32]; mine += cnt8[i]; }
+            unsigned incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned up = __shfl_up_sync(cm::kFullMask, incl, o);
+                if (lane >= o) incl += up;
+            }
+            const unsigned reached = __ballot_sync(cm::kFullMask, incl >= rem);
+            const int owner = reached ? __ffs(reached) - 1 : 31;
+            if (lane == owner) {
+                unsigned acc = incl - mine;
+                int b = first - 7;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    if (acc + cnt8[i] >= rem) { b = first - i; break; }
+                    if (i < 7) acc += cnt8[i];
+                }
+                if (b < 0) b = 0;
+                s_rem = rem - acc;
+                s_prefix = prefix | ((uint32_t)b << shift);
+            }
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const float kth = float_of_key(s_prefix);
+        tau[blockIdx.x] = (kth == kth) ? kth - band : -__int_as_float(0x7f800000);    // fewer than k valid cosines: everything passes
+    }
+}
+
+// Exact cosine of `row` against the query held in q[] -- the lane layout, FMA order and reduction tree of the one-query
+// scans (cm_scan16_kernel: 16 lanes x 5 float4, xor tree 8,4,2,1; cm_scan_kernel: 32 lanes, xor tree 16..1).
+template <int LPG, int VPL>
+__device__ __forceinline__ float exact_cosine(const float4 *__restrict__ t4, int dim4, int64_t row, const float4 (&q)[VPL],
+                                              int sub, float norm) {
+    float4 buf[VPL];
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+        const int j = sub + LPG * v;
+        buf[v] = j < dim4 ? __ldg(t4 + row * dim4 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+        if (LPG == 32 && sub + LPG * v >= dim4) continue;            // the 32-lane scan skips absent pieces, the 16-lane one adds zeros
+        s = fmaf(buf[v].x, q[v].x, s); s = fmaf(buf[v].y, q[v].y, s);
+        s = fmaf(buf[v].z, q[v].z, s); s = fmaf(buf[v].w, q[v].w, s);
+    }
+#pragma unroll
+    for (int o = LPG / 2; o > 0; o >>= 1) s += __shfl_xor_sync(cm::kFullMask, s, o);
+    return s / norm;
+}
+
+// Candidates re-scored exactly; blockIdx.y = query, its candidates dealt round-robin to the kRescoreCtas x (512 / LPG)
+// lane groups of the grid's row: keys[q][i] = (~key(cosine), row).
+constexpr int kRescoreCtas = 16, kRescoreThreads = 512;
+
+template <int LPG, int VPL>
+__global__ void __launch_bounds__(kRescoreThreads)
+cm_rescore_kernel(const float *__restrict__ table, int dim4, const float *__restrict__ mean, const float *__restrict__ norms,
+                  const int32_t *__restrict__ cand, const unsigned *__restrict__ cnt, unsigned long long *__restrict__ keys) {
+    const int q_id = blockIdx.y;
+    const unsigned n = cnt[q_id];
+    constexpr unsigned kGroups = kRescoreThreads / LPG;
+    if (n > kCandCap || blockIdx.x * kGroups >= n) return;
+    const int lane = threadIdx.x & 31, sub = lane & (LPG - 1);
+    const float4 *t4 = reinterpret_cast<const float4 *>(table);
+    float4 q[VPL];
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+        const int j = sub + LPG * v;
+        q[v] = j < dim4 ? reinterpret_cast<const float4 *>(mean + (size_t)q_id * dim4 * 4)[j] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    // whole warps stay in the loop (the reduction shuffles): the bound is per warp, the tail lanes score row 0 unused
+    const unsigned warp_first = blockIdx.x * kGroups + (threadIdx.x >> 5) * (32 / LPG);
+    for (unsigned base = warp_first; base < n; base += kRescoreCtas * kGroups) {
+        const unsigned i = base + (unsigned)(lane / LPG);
+        const bool have = i < n;
+        const int32_t row = have ? cand[(size_t)q_id * kCandCap + i] : 0;
+        const float d = exact_cosine<LPG, VPL>(t4, dim4, row, q, sub, norms[row]);
+        if (have && sub == 0) keys[(size_t)q_id * kCandCap + i] = ((unsigned long long)(~cm::similar_key_of(d)) << 32) | (uint32_t)row;
+    }
+}
+
+// One CTA per query: sort its candidates (cosine desc, row asc), write the best k.
+// n_out[q] = k, or -1 when the candidates overflowed kCandCap or fewer than k were collected (the host then
+// runs the one-query path for q).
+__global__ void __launch_bounds__(1024)
+cm_topk_kernel(const unsigned long long *__restrict__ keys, const unsigned *__restrict__ cnt, unsigned k,
+               int32_t *__restrict__ rows_out, float *__restrict__ sims_out, int *__restrict__ n_out) {
+    extern __shared__ unsigned long long s_keys[];                   // up to kCandCap entries
+    const int q_id = blockIdx.x;
+    const unsigned n = cnt[q_id];
+    if (n > kCandCap || n < k) {
+        if (threadIdx.x == 0) n_out[q_id] = -1;
+        return;
+    }
+    unsigned size = 64;
+    while (size < n) size <<= 1;
+    for (unsigned i = threadIdx.x; i < size; i += blockDim.x) s_keys[i] = i < n ? keys[(size_t)q_id * kCandCap + i] : ~0ull;
+    __syncthreads();
+    for (unsigned span = 2; span <= size; span <<= 1) {              // bitonic, ascending = best first
+        for (unsigned stride = span >> 1; stride > 0; stride >>= 1) {
+            for (unsigned c = threadIdx.x; c < size / 2; c += blockDim.x) {
+                const unsigned lo = 2 * c - (c & (stride - 1));
+                const unsigned hi = lo + stride;
+                const bool up = (lo & span) == 0;
+                const unsigned long long x = s_keys[lo], y = s_keys[hi];
+                if ((x > y) == up) { s_keys[lo] = y; s_keys[hi] = x; }
+            }
+            __syncthreads();
+        }
+    }
+    for (unsigned i = threadIdx.x; i < k; i += blockDim.x) {
+        const unsigned long long e = s_keys[i];
+        rows_out[(size_t)q_id * cm::kSimilarMaxTopK + i] = (int32_t)(e & 0xffffffffull);
+        sims_out[(size_t)q_id * cm::kSimilarMaxTopK + i] = float_of_key(~(uint32_t)(e >> 32));
+    }
+    if (threadIdx.x == 0) n_out[q_id] = (int)k;
+}
+
+}  // namespace
+
+// ---- host side -------------------------------------------------------------------------------------
+struct cm_similar_batch {
+    float *d_mean = nullptr;             // [kMaxNQ][dim]
+    int32_t *d_rows = nullptr;           // [kMaxNQ]
+    float *d_tau = nullptr;              // [kMaxNQ]
+    unsigned *d_cnt = nullptr;           // [kMaxNQ]
+    unsigned *d_err = nullptr;
+    int32_t *d_cand = nullptr;           // [kMaxNQ][kCandCap]
+    unsigned long long *d_keys = nullptr; // [kMaxNQ][kCandCap] exact (~key, row) of the candidates
+    float *d_sample = nullptr;           // [kMaxNQ][sample_ld]
+    float *d_padded = nullptr;           // experiment: the table with rows padded to a multiple of 128 bytes
+    int64_t padded_rows = 0;
+    size_t sample_floats = 0;
+    unsigned char *h_result = nullptr;   // page-locked: rows [kMaxNQ][1024] | sims [kMaxNQ][1024] | n [kMaxNQ] | err
+    CUtensorMap map_table;
+    const float *map_table_ptr = nullptr;
+    int64_t map_table_rows = 0;
+    int sm_count = 148;
+    bool attrs_set = false;
+};
+
+namespace {
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            p = nullptr;
+        }
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+// [n_rows][dim] fp32, row-major; boxes of box_rows x 32 floats in the 128-byte swizzle, columns past dim read as zero
+int make_map(CUtensorMap *map, const float *base, int64_t n_rows, int dim, int box_rows, int pitch = 0) {
+    EncodeTiledFn fn = encode_tiled();
+    if (fn == nullptr) return fail(CM_ERR_CUDA, "the driver does not export cuTensorMapEncodeTiled");
+    const cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)n_rows};
+    const cuuint64_t gstride[1] = {(cuuint64_t)(pitch > 0 ? pitch : dim) * sizeof(float)};
+    const cuuint32_t box[2] = {(cuuint32_t)kChunkFloats, (cuuint32_t)box_rows};
+    const cuuint32_t estride[2] = {1, 1};
+    static const int promo = [] { const char *v = getenv("CM_SIMBATCH_L2PROMO"); return v ? atoi(v) : 3; }();
+    const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), gdim, gstride, box, estride,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, (CUtensorMapL2promotion)promo,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(CM_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return CM_OK;
+}
+
+constexpr size_t kSmemLimit = 232448;                  // 227 KB, the most one CTA may have
+constexpr size_t kScanSmemFixed = 1024 + kMaxNQ * 4 + 32 * 8;
+
+// A-ring depth that fits beside the query block
+int scan_stages(int nq, int n_chunks) {
+    const size_t left = kSmemLimit - kScanSmemFixed - (size_t)n_chunks * nq * 128;
+    const int st = (int)(left / kStageBytes);
+    return st > kMaxStages ? kMaxStages : st;
+}
+size_t scan_smem(int nq, int n_chunks, int stages) { return kScanSmemFixed + (size_t)n_chunks * nq * 128 + (size_t)stages * kStageBytes; }
+constexpr size_t kResultRows = (size_t)kMaxNQ * cm::kSimilarMaxTopK;
+
+int batch_state(cm_engine *e, cm_similar_state *s, cm_similar_batch **out) {
+    if (s->batch == nullptr) {
+        cm_similar_batch *b = new (std::nothrow) cm_similar_batch();
+        if (b == nullptr) return fail(CM_ERR_NOMEM, "most_similar batch state allocation failed");
+        s->batch = b;
+        cudaError_t err = cudaMalloc(&b->d_mean, (size_t)kMaxNQ * e->dim * sizeof(float));
+        if (err == cudaSuccess) err = cudaMalloc(&b->d_rows, kMaxNQ * sizeof(int32_t));
+        if (err == cudaSuccess) err = cudaMalloc(&b->d_tau, kMaxNQ * sizeof(float));
+        if (err == cudaSuccess) err = cudaMalloc(&b->d_cnt, kMaxNQ * sizeof(unsigned));
+        if (err == cudaSuccess) err = cudaMalloc(&b->d_err, sizeof(unsigned));
+        if (err == cudaSuccess) err = cudaMemset(b->d_err, 0, sizeof(unsigned));
+        if (err == cudaSuccess) err = cudaMalloc(&b->d_cand, (size_t)kMaxNQ * kCandCap * sizeof(int32_t));
+        if (err == cudaSuccess) err = cudaMalloc(&b->d_keys, (size_t)kMaxNQ * kCandCap * sizeof(unsigned long long));
+        if (err == cudaSuccess) err = cudaHostAlloc(&b->h_result, kResultRows * 8 + kMaxNQ * sizeof(int), cudaHostAllocDefault);
+        if (err == cudaSuccess) {
+            int sms = 0;
+            if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device) == cudaSuccess && sms > 0) b->sm_count = sms;
+        }
+        if (err != cudaSuccess) {
+            cudaGetLastError();
+            cm::similar_batch_free(s);
+            return fail(CM_ERR_NOMEM, "most_similar batch scratch failed: %s", cudaGetErrorString(err));
+        }
+    }
+    *out = s->batch;
+    return CM_OK;
+}
+
+template <int LPG, int VPL>
+void launch_rescore(cm_engine *e, cm_similar_state *s, cm_similar_batch *b, int n_real) {
+    const dim3 grid(kRescoreCtas, (unsigned)n_real);
+    cm_rescore_kernel<LPG, VPL><<<grid, kRescoreThreads, 0, e->stream>>>(e->d_table, e->dim / 4, b->d_mean, s->d_norms, b->d_cand, b->d_cnt, b->d_keys);
+    cm::count_launch();
+}
+
+}  // namespace
+
+void cm::similar_batch_free(cm_similar_state *s) {
+    cm_similar_batch *b = s->batch;
+    if (b == nullptr) return;
+    void *ptrs[] = {b->d_mean, b->d_rows, b->d_tau, b->d_cnt, b->d_err, b->d_cand, b->d_keys, b->d_sample, b->d_padded};
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    if (b->h_result) cudaFreeHost(b->h_result);
+    delete b;
+    s->batch = nullptr;
+}
+
+extern "C" int cm_most_similar_batch(cm_engine *e, const int32_t *rows, int n_queries, int k,
+                                     int32_t *rows_out, float *sims_out, int *n_out) {
+    if (int rc = cm::check_engine(e)) return rc;
+    if (n_queries < 0) return fail(CM_ERR_INVALID, "n_queries %d is negative", n_queries);
+    if (k < 1 || k > cm::kSimilarMaxTopK) return fail(CM_ERR_INVALID, "k %d outside [1, %d]", k, cm::kSimilarMaxTopK);
+    if (n_queries == 0) return CM_OK;
+    if (!rows || !rows_out || !sims_out || !n_out) return fail(CM_ERR_INVALID, "a buffer pointer is NULL");
+    for (int q = 0; q < n_queries; ++q)
+        if (rows[q] < 0 || (int64_t)rows[q] >= e->n_rows)
+            return fail(CM_ERR_INVALID, "rows[%d] = %d outside the %lld-row table", q, rows[q], (long long)e->n_rows);
+    std::lock_guard<std::mutex> lock(e->mu);
+    cm::DeviceGuard guard(e->device);
+    cm_similar_state *s = nullptr;
+    if (int rc = cm::similar_prepare(e, &s)) return rc;
+    const unsigned kk = (unsigned)((int64_t)k < e->n_rows ? k : e->n_rows);
+    // Test hook / escape hatch: CM_SIMILAR_BATCH=0 runs the queries one by one.
+    static const bool batch_off = [] { const char *v = getenv("CM_SIMILAR_BATCH"); return v != nullptr && *v == '0'; }();
+    const bool tensor_path = !batch_off && n_queries >= 2 && e->dim % 4 == 0 && e->dim <= kMaxChunks * kChunkFloats;
+    if (!tensor_path) {
+        for (int q = 0; q < n_queries; ++q)
+            if (int rc = cm::most_similar_locked(e, rows[q], k, rows_out + (size_t)q * k, sims_out + (size_t)q * k, n_out + q)) return rc;
+        return CM_OK;
+    }
+    cm_similar_batch *b = nullptr;
+    if (int rc = batch_state(e, s, &b)) return rc;
+    cudaStream_t st = e->stream;
+    if (!b->attrs_set) {
+        CM_CUDA(cudaFuncSetAttribute(cm_simscan_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLimit));
+        CM_CUDA(cudaFuncSetAttribute(cm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kCandCap * sizeof(unsigned long long))));
+        b->attrs_set = true;
+    }
+    static const bool padded = [] { const char *v = getenv("CM_SIMBATCH_PADDED"); return v != nullptr && *v == '1'; }();
+    if (b->map_table_ptr != e->d_table || b->map_table_rows != e->n_rows || (padded && s->batch_table_stale)) {
+        if (padded) {
+            const int pitch = (e->dim + kChunkFloats - 1) / kChunkFloats * kChunkFloats;
+            if (b->padded_rows != e->n_rows) {
+                if (b->d_padded) cudaFree(b->d_padded);
+                b->d_padded = nullptr;
+                b->padded_rows = 0;
+                CM_CUDA(cudaMalloc(&b->d_padded, (size_t)e->n_rows * pitch * sizeof(float)));
+                b->padded_rows = e->n_rows;
+            }
+            cm_pad_rows_kernel<<<148 * 8, 256, 0, st>>>(reinterpret_cast<const float4 *>(e->d_table), e->n_rows, e->dim / 4, pitch / 4,
+                                                       reinterpret_cast<float4 *>(b->d_padded));
+            cm::count_launch();
+            if (int rc = make_map(&b->map_table, b->d_padded, e->n_rows, e->dim, kTileRows, pitch)) return rc;
+            s->batch_table_stale = false;
+        } else if (int rc = make_map(&b->map_table, e->d_table, e->n_rows, e->dim, kTileRows)) {
+            return rc;
+        }
+        b->map_table_ptr = e->d_table;
+        b->map_table_rows = e->n_rows;
+    }
+    // the sample: every S-th tile, S chosen so that the k-th largest of the sample admits about k * S candidates
+    const int n_tiles = (int)((e->n_rows + kTileRows - 1) / kTileRows);
+    int stride = n_tiles / 512;
+    if (stride > 2048 / (int)kk) stride = 2048 / (int)kk;
+    if (stride > 64) stride = 64;
+    if (stride < 1) stride = 1;
+    const int n_sample_visits = (n_tiles + stride - 1) / stride;
+    const int64_t sample_ld = (int64_t)n_sample_visits * kTileRows;
+    if (b->sample_floats < (size_t)sample_ld * kMaxNQ) {
+        if (b->d_sample) cudaFree(b->d_sample);
+        b->d_sample = nullptr;
+        b->sample_floats = 0;
+        CM_CUDA(cudaMalloc(&b->d_sample, (size_t)sample_ld * kMaxNQ * sizeof(float)));
+        b->sample_floats = (size_t)sample_ld * kMaxNQ;
+    }
+    int32_t *h_rows = reinterpret_cast<int32_t *>(b->h_result);
+    float *h_sims = reinterpret_cast<float *>(b->h_result + kResultRows * 4);
+    int *h_n = reinterpret_cast<int *>(b->h_result + kResultRows * 8);
+    const int dim4 = e->dim / 4;
+    for (int q0 = 0; q0 < n_queries; q0 += kMaxNQ) {
+        const int n_real = n_queries - q0 < kMaxNQ ? n_queries - q0 : kMaxNQ;
+        const int nq = (n_real + 15) / 16 * 16;
+        CM_CUDA(cudaMemcpyAsync(b->d_rows, rows + q0, n_real * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        CM_CUDA(cudaMemsetAsync(b->d_cnt, 0, kMaxNQ * sizeof(unsigned), st));
+        cm_query_batch_kernel<<<nq, 32, 0, st>>>(e->d_table, e->dim, b->d_rows, n_real, s->d_norms, b->d_mean);
+        cm::count_launch();
+        CUtensorMap map_q;
+        if (int rc = make_map(&map_q, b->d_mean, nq, e->dim, nq)) return rc;
+        ScanArgs a = {};
+        a.norms = s->d_norms;
+        a.n_rows = e->n_rows;
+        a.nq = nq;
+        a.dim = e->dim;
+        a.sample_out = b->d_sample;
+        a.sample_ld = sample_ld;
+        a.tau = b->d_tau;
+        a.cand = b->d_cand;
+        a.cnt = b->d_cnt;
+        a.err = b->d_err;
+        const int n_chunks = (e->dim + kChunkFloats - 1) / kChunkFloats;
+        a.stages = scan_stages(nq, n_chunks);
+        const size_t smem = scan_smem(nq, n_chunks, a.stages);
+        // sample pass
+        a.mode = 0;
+        a.n_visits = n_sample_visits;
+        a.tile_stride = stride;
+        int grid = n_sample_visits < b->sm_count ? n_sample_visits : b->sm_count;
+        cm_simscan_tc_kernel<<<grid, kScanThreads, smem, st>>>(b->map_table, map_q, a);
+        cm::count_launch();
+        cm_kth_kernel<<<nq, 1024, 0, st>>>(b->d_sample, sample_ld, sample_ld, kk, kBand, b->d_tau, n_real);
+        cm::count_launch();
+        // full pass
+        a.mode = 1;
+        a.n_visits = n_tiles;
+        a.tile_stride = 1;
+        grid = n_tiles < b->sm_count ? n_tiles : b->sm_count;
+        cm_simscan_tc_kernel<<<grid, kScanThreads, smem, st>>>(b->map_table, map_q, a);
+        cm::count_launch();
+        if (cm::similar_uses_scan16(dim4)) launch_rescore<16, 5>(e, s, b, n_real);
+        else if (dim4 <= 32) launch_rescore<32, 1>(e, s, b, n_real);
+        else if (dim4 <= 64) launch_rescore<32, 2>(e, s, b, n_real);
+        else launch_rescore<32, 3>(e, s, b, n_real);
+        cm_topk_kernel<<<n_real, 1024, kCandCap * sizeof(unsigned long long), st>>>(b->d_keys, b->d_cnt, kk, h_rows, h_sims, h_n);
+        cm::count_launch();
+        CM_CUDA(cudaGetLastError());
+        const cudaError_t sync = cudaStreamSynchronize(st);
+        if (sync != cudaSuccess)
+            return fail(CM_ERR_CUDA, "most_similar batch scan failed: %s (a pipeline wait inside the kernel may have timed out)",
+                        cudaGetErrorString(sync));
+        for (int q = 0; q < n_real; ++q) {
+            int32_t *ro = rows_out + (size_t)(q0 + q) * k;
+            float *so = sims_out + (size_t)(q0 + q) * k;
+            if (h_n[q] >= 0) {
+                memcpy(ro, h_rows + (size_t)q * cm::kSimilarMaxTopK, kk * sizeof(int32_t));
+                memcpy(so, h_sims + (size_t)q * cm::kSimilarMaxTopK, kk * sizeof(float));
+                n_out[q0 + q] = h_n[q];
+            } else if (int rc = cm::most_similar_locked(e, rows[q0 + q], k, ro, so, n_out + q0 + q)) {
+                return rc;
+            }
+        }
+    }
+    return CM_OK;
+}

@@ -146,6 +146,17 @@ class ScoringEngine:
                                         ctypes.byref(n)))
         return rows[: n.value], sims[: n.value]
 
+    def most_similar_batch(self, rows, k: int):
+        """``most_similar(row, k)`` for every row of ``rows`` in one pass over the table (C ABI
+        cm_most_similar_batch): a list of (rows, sims) pairs, identical to the one-query results."""
+        q = np.ascontiguousarray(rows, dtype=np.int32).reshape(-1)
+        out_rows = np.empty((q.size, k), dtype=np.int32)
+        out_sims = np.empty((q.size, k), dtype=np.float32)
+        n = np.zeros(q.size, dtype=np.int32)
+        check(self._lib.cm_most_similar_batch(self._h, q.ctypes.data, int(q.size), int(k), out_rows.ctypes.data,
+                                              out_sims.ctypes.data, n.ctypes.data))
+        return [(out_rows[i, : n[i]].copy(), out_sims[i, : n[i]].copy()) for i in range(q.size)]
+
     def score_device(self, d_guess_idx: int, d_guess_len: int, n_guesses: int, n_slots: int,
                      d_answer_slot: int, d_exact: int, min_score: float, d_scores: int,
                      d_centi: int = 0, stream: Optional[int] = None, flags: int = 0) -> None:

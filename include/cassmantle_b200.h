@@ -242,6 +242,18 @@ int cm_score_words_host(cm_engine *e, cm_vocab *v,
  * norms (gensim's fill_norms).  NaN cosines rank last.                                       */
 int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_out, float *sims_out, int *n_out);
 
+/* The same for n_queries words in ONE pass over the table (an extension for the micro-batcher: the
+ * reference calls most_similar once per word).  rows[q] is query q's table row; its k best land in
+ * rows_out / sims_out [q * k .. q * k + n_out[q]), exactly what cm_most_similar(rows[q], k) returns --
+ * the same rows and the same fp32 cosines (entries tied at the k-th place may resolve differently).
+ * Up to 64 queries share a pass: the table is multiplied with the query block on the tensor cores in
+ * tf32 only to FILTER candidates (threshold from a sampled pass, widened by the tf32 error bound), and
+ * the candidates are re-scored with the one-query arithmetic.  Tables wider than 320 columns, a single
+ * query, or CM_SIMILAR_BATCH=0 in the environment take the one-query path in a loop.  Host pointers,
+ * blocking.                                                                                      */
+int cm_most_similar_batch(cm_engine *e, const int32_t *rows, int n_queries, int k,
+                          int32_t *rows_out, float *sims_out, int *n_out);
+
 /* ---- mask selection, numeric half ------------------------------------- *
  * semantic_distance(word, word_list, model), src/utils.py:73-79, for every word of word_list
  * at once (select_descriptive_words calls it in a loop, src/utils.py:91):

@@ -181,3 +181,83 @@ def test_16_lane_scan_agrees_with_the_generic_scan():
 
 def test_16_lane_scan_agrees_with_the_generic_scan_at_full_size():
     _compare_scans(synth.FULL_ROWS, [(2_718_281, 51), (7, 200)])
+
+
+# ---- cm_most_similar_batch: many queries per pass over the table (tensor-core filter + exact re-score) ----
+def _same_as_single(eng, queries, k):
+    batch = eng.most_similar_batch(queries, k)
+    assert len(batch) == len(queries)
+    for q, (rows, sims) in zip(queries, batch):
+        want_rows, want_sims = eng.most_similar(int(q), k)
+        assert np.array_equal(sims, want_sims), (q, k)              # the same fp32 cosines, bit for bit
+        inside = sims > sims[-1]                                    # entries tied at the k-th place may differ
+        assert np.array_equal(rows[inside], want_rows[inside]), (q, k)
+        assert len(set(rows.tolist())) == len(rows)
+
+
+def test_batch_equals_single_queries(small_engine, small_table):
+    rng = np.random.default_rng(5)
+    for n_q, k in ((2, 11), (16, 51), (37, 1), (64, 11), (70, 11), (5, 1024)):
+        queries = rng.integers(0, small_table.shape[0], size=n_q).astype(np.int32)
+        _same_as_single(small_engine, queries, k)
+
+
+def test_batch_matches_oracle(small_engine, small_table):
+    queries = np.array([0, 123, 49_999, 31337, 123], dtype=np.int32)    # a repeated query is allowed
+    for k in (11, 200):
+        for q, (rows, sims) in zip(queries, small_engine.most_similar_batch(queries, k)):
+            _check(rows, sims, O.most_similar_dists(small_table, int(q)), k, int(q))
+
+
+def test_batch_other_widths_and_small_tables():
+    from cassmantle_b200.engine import ScoringEngine
+    rng = np.random.default_rng(11)
+    for n_rows, dim in ((300, 300), (5000, 64), (4097, 128), (2000, 200), (1500, 320), (900, 324)):
+        vec = rng.standard_normal((n_rows, dim)).astype(np.float32)
+        vec[7] = vec[3]                                              # a duplicated row: an exact tie
+        with ScoringEngine.from_vectors(vec) as eng:
+            queries = np.array([3, 7, n_rows - 1, 0, 11], dtype=np.int32)
+            for k in (1, 10, min(300, n_rows)):
+                _same_as_single(eng, queries, k)
+                for q, (rows, sims) in zip(queries, eng.most_similar_batch(queries, k)):
+                    # rows 3 and 7 are copies: at k = 1 either of them is "the" best row
+                    _check(rows, sims, O.most_similar_dists(vec, int(q)), k, 3 if int(q) == 7 and k == 1 else int(q))
+
+
+def test_batch_special_rows_fall_back():
+    """NaN rows, zero rows and a crowd of duplicates: candidates overflow or run short and the query is finished
+    by the one-query path -- results still equal it."""
+    from cassmantle_b200.engine import ScoringEngine
+    rng = np.random.default_rng(3)
+    vec = rng.standard_normal((20_000, 300)).astype(np.float32)
+    vec[100] = 0.0
+    vec[200, 5] = np.nan
+    vec[1000:11_000] = vec[1000]                                     # 10,000 copies: more candidates than the cap
+    with ScoringEngine.from_vectors(vec) as eng:
+        queries = np.array([1000, 5, 100, 6, 200], dtype=np.int32)
+        for k in (3, 50):
+            batch = eng.most_similar_batch(queries, k)
+            for q, (rows, sims) in zip(queries, batch):
+                want_rows, want_sims = eng.most_similar(int(q), k)
+                assert np.array_equal(sims, want_sims, equal_nan=True), (q, k)
+
+
+def test_batch_argument_errors(small_engine):
+    from cassmantle_b200._lib import CassMantleError
+    with pytest.raises(CassMantleError):
+        small_engine.most_similar_batch([0, 10**9], 5)
+    with pytest.raises(CassMantleError):
+        small_engine.most_similar_batch([0, 1], 0)
+    assert small_engine.most_similar_batch([], 5) == []
+
+
+def test_backend_most_similar_many(small_engine, small_table):
+    from cassmantle_b200.backend import Backend
+    from cassmantle_b200.vocab import Vocabulary
+    keys = synth.make_vocab(small_table.shape[0])
+    be = Backend(small_engine, Vocabulary(keys), min_score=0.01)
+    words = [keys[5].upper(), keys[777], keys[4242]]
+    many = be.most_similar_many(words, topn=20)
+    assert many == [be.most_similar(w, topn=20) for w in words]
+    with pytest.raises(Exception):
+        be.most_similar_many(["no-such-word"], topn=5)
