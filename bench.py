@@ -1041,6 +1041,33 @@ def run_own(args) -> None:
         eng.set_answers(ans)
         eng.synchronize()
 
+    # ---- most_similar over the same table: one query per pass and many (the tensor-core path) ----
+    similar = None
+    if rank == 0 and world == 1 and not args.no_other_shapes:
+        rng = np.random.default_rng(9)
+        eng.most_similar(1, 51)                                  # also computes the row norms, once
+        ts1 = []
+        for q in rng.integers(0, V, size=12):
+            t1 = time.perf_counter(); one = eng.most_similar(int(q), 51); ts1.append(time.perf_counter() - t1)
+        queries = rng.integers(0, V, size=128).astype(np.int32)
+        got = eng.most_similar_batch(queries, 51)
+        tsb = []
+        for _ in range(5):
+            t1 = time.perf_counter(); got = eng.most_similar_batch(queries, 51); tsb.append(time.perf_counter() - t1)
+        same = True
+        for q, (rows_b, sims_b) in list(zip(queries, got))[:8]:
+            rows_1, sims_1 = eng.most_similar(int(q), 51)
+            same = same and bool(np.array_equal(sims_b, sims_1)) and bool(np.array_equal(rows_b[sims_b > sims_b[-1]], rows_1[sims_1 > sims_1[-1]]))
+        one_us = float(np.median(ts1)) * 1e6
+        batch_us = float(np.median(tsb)) * 1e6
+        similar = {"workload": "most_similar(topn=50) over the 3,000,000 x 300 table, blocking calls from Python",
+                   "one_query_us": one_us, "one_query_frac_of_hbm_peak": (V * (D * 4 + 8)) / (one_us * 1e-6) / 1e9 / peak,
+                   "batch_128_queries_us": batch_us, "batch_us_per_query": batch_us / 128,
+                   "batch_identical_to_one_query_calls": same,
+                   "batch_path": "cm_most_similar_batch: tcgen05 tf32 scan (TMA, TMEM) as a filter + exact fp32 re-score"}
+        eng.set_answers(ans)
+        eng.synchronize()
+
     clocks = dict(timed_clocks, remeasured=bool(attempt))
 
     # ---- parity spot check of the timed path against the CPU sample ----------------------
@@ -1072,7 +1099,7 @@ def run_own(args) -> None:
             "sustained": sustained,
             "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
             "cpu_baseline": cpu_baseline, "clocks": clocks, "latency": lat, "parity": parity,
-            "other_shapes": other, "python_boundary": py_lat,
+            "other_shapes": other, "python_boundary": py_lat, "most_similar": similar,
         }
         print(json.dumps(line), flush=True)
     if gather is not None:

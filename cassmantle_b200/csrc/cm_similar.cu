@@ -628,6 +628,6 @@ int cm::most_similar_locked(cm_engine *e, int32_t row, int k, int32_t *rows_out,
 // The table changed (upload / synthetic fill): the cached row norms are stale.
 namespace cm {
 void similar_invalidate(cm_engine *e) {
-    if (e->similar) { e->similar->norms_ready = false; e->similar->batch_table_stale = true; }
+    if (e->similar) e->similar->norms_ready = false;
 }
 }  // namespace cm

@@ -16,9 +16,9 @@
 //                            mode 0  sample pass over every S-th tile: approximate cosines written out,
 //                                    cm_kth_kernel takes the k-th largest per query as threshold tau_q
 //                            mode 1  full pass: every (row, q) with cosine >= tau_q - band is a candidate
-//   cm_rescore_kernel      candidates re-scored in fp32 with exactly the arithmetic of the one-query scan
-//                          (same lanes, same FMA order, dot / norm)
-//   cm_topk_kernel         per query: sorted (cosine desc, row asc), top k out.
+//   cm_finish_kernel       per query: candidates cut down to those within the error band of the k-th largest tf32
+//                          cosine, re-scored in fp32 with exactly the arithmetic of the one-query scan (same lanes,
+//                          same FMA order, dot / norm), sorted (cosine desc, row asc), top k out.
 // The k-th largest of a sample is a lower bound of the k-th largest overall, and the band covers the tf32
 // error on both sides, so every true top-k row is among the candidates: rows and cosines are those of Q
 // calls of cm_most_similar, bit for bit (ties at the k-th place may resolve differently, as they may there).
@@ -47,7 +47,7 @@ constexpr int kStageBytes = kTileRows * kChunkFloats * 4;
 constexpr int kMaxNQ = 128;             // queries per pass (UMMA N)
 constexpr int kTmemCols = 256;          // two accumulators of kMaxNQ columns
 constexpr int kScanThreads = 320;        // TMA warp, MMA warp, eight epilogue warps
-constexpr unsigned kCandCap = 8192;     // candidates per query the re-score kernel sorts in shared memory
+constexpr unsigned kCandCap = 16384;    // candidates per query the full pass may collect
 // tf32 keeps 10 mantissa bits (truncation): each product is off by < 2^-9 relative, so a cosine (unit query,
 // division by the row norm) by < 2^-9 absolute.  Threshold and candidate are both approximate: 2 x 2^-9.
 constexpr float kBand = 4.0e-3f;
@@ -136,7 +136,7 @@ struct ScanArgs {
     float *sample_out;       // [nq][sample_ld]
     int64_t sample_ld;
     const float *tau;        // [nq] thresholds, band already subtracted
-    int32_t *cand;           // [nq][kCandCap]
+    unsigned long long *cand; // [nq][kCandCap]: (key of the tf32 cosine) << 32 | row
     unsigned *cnt;           // [nq]
     unsigned *err;
 };
@@ -284,7 +284,8 @@ cm_simscan_tc_kernel(const __grid_constant__ CUtensorMap map_table, const __grid
                         const int i = __ffs(hits) - 1;
                         hits &= hits - 1u;
                         const unsigned slot = atomicAdd(a.cnt + c0 + i, 1u);
-                        if (slot < kCandCap) a.cand[(size_t)(c0 + i) * kCandCap + slot] = (int32_t)row;
+                        if (slot < kCandCap)
+                            a.cand[(size_t)(c0 + i) * kCandCap + slot] = ((unsigned long long)cm::similar_key_of(d[i]) << 32) | (uint32_t)row;
                     }
                 }
             }
@@ -328,53 +329,34 @@ __global__ void cm_query_batch_kernel(const float *__restrict__ table, int dim, 
     }
 }
 
-// experiment: rows re-pitched to `pitch4` float4 (a multiple of 128 bytes), zero-filled past dim4
-__global__ void __launch_bounds__(256)
-cm_pad_rows_kernel(const float4 *__restrict__ table, int64_t n_rows, int dim4, int pitch4, float4 *__restrict__ out) {
-    const int64_t total = n_rows * pitch4;
-    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
-        const int64_t r = i / pitch4;
-        const int j = (int)(i % pitch4);
-        out[i] = j < dim4 ? table[r * dim4 + j] : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-}
-
 __device__ __forceinline__ float float_of_key(uint32_t key) {        // inverse of similar_key_of (NaN was 0)
     if (key == 0u) return __int_as_float(0x7fc00000);
     return __uint_as_float((key & 0x80000000u) ? (key & 0x7fffffffu) : ~key);
 }
 
-// tau[q] = (k-th largest of the n sampled cosines of query q) - band; one CTA per query, 4-pass radix select.
-__global__ void __launch_bounds__(1024)
-cm_kth_kernel(const float *__restrict__ sample, int64_t ld, int64_t n, unsigned k, float band, float *__restrict__ tau, int n_real) {
-    __shared__ unsigned hist[256 * 32];                               // [bin][lane]: a warp's 32 adds never share a bank
-    __shared__ uint32_t s_prefix;
-    __shared__ unsigned s_rem;
-    const float *d = sample + (int64_t)blockIdx.x * ld;
-    if ((int)blockIdx.x >= n_real) {                                  // padding up to the UMMA N: nothing is a candidate
-        if (threadIdx.x == 0) tau[blockIdx.x] = __int_as_float(0x7f800000);
-        return;
-    }
-    if (threadIdx.x == 0) { s_prefix = 0u; s_rem = k; }
-    for (int pass = 0; pass < 4; ++pass) {
+// The top 8 * PASSES bits of the k-th largest of key_at(0 .. n), the rest zero (so: a lower bound of that key that at
+// least k keys reach).  Radix select from the top, 8 bits per pass; called by every thread of the CTA.
+// hist: 256 x 32 counters in shared memory -- [bin][lane], so the 32 adds of a warp never share a bank.
+template <int PASSES, class KeyAt>
+__device__ uint32_t block_kth_prefix(KeyAt key_at, int64_t n, unsigned k, unsigned *hist, uint32_t *s_prefix, unsigned *s_rem) {
+    if (threadIdx.x == 0) { *s_prefix = 0u; *s_rem = k; }
+    for (int pass = 0; pass < PASSES; ++pass) {
         for (int i = threadIdx.x; i < 256 * 32; i += blockDim.x) hist[i] = 0u;
         __syncthreads();
-        const uint32_t prefix = s_prefix;
+        const uint32_t prefix = *s_prefix;
         const uint32_t mask = pass == 0 ? 0u : (0xffffffffu << (32 - 8 * pass));
         const int shift = 24 - 8 * pass;
         for (int64_t i0 = threadIdx.x; i0 < n; i0 += 8 * (int64_t)blockDim.x) {     // eight loads in flight per thread
-            float x[8];
+            uint32_t key[8];
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
                 const int64_t i = i0 + u * (int64_t)blockDim.x;
-                x[u] = i < n ? __ldcg(d + i) : __int_as_float(0x7fc00000);
+                key[u] = i < n ? key_at(i) : 0u;
             }
 #pragma unroll
-            for (int u = 0; u < 8; ++u) {
-                const uint32_t key = cm::similar_key_of(x[u]);
-                if (i0 + u * (int64_t)blockDim.x < n && (key & mask) == prefix)
-                    atomicAdd(&hist[((key >> shift) & 0xffu) * 32 + (threadIdx.x & 31)], 1u);
-            }
+            for (int u = 0; u < 8; ++u)
+                if (i0 + u * (int64_t)blockDim.x < n && (key[u] & mask) == prefix)
+                    atomicAdd(&hist[((key[u] >> shift) & 0xffu) * 32 + (threadIdx.x & 31)], 1u);
         }
         __syncthreads();
         if (threadIdx.x < 256) {                                      // fold the 32 copies into copy 0
@@ -387,7 +369,7 @@ cm_kth_kernel(const float *__restrict__ sample, int64_t ld, int64_t n, unsigned 
         if (threadIdx.x < 32) {                                       // which bin, from the top, holds the rem-th entry
             const int lane = threadIdx.x;
             const int first = 255 - 8 * lane;                         // this lane's bins: first, first - 1, ..., first - 7
-            const unsigned rem = s_rem;
+            const unsigned rem = *s_rem;
             unsigned cnt8[8], mine = 0;
 #pragma unroll
             for (int i = 0; i < 8; ++i) { cnt8[i] = hist[(first - i) * 32]; mine += cnt8[i]; }
@@ -407,15 +389,30 @@ cm_kth_kernel(const float *__restrict__ sample, int64_t ld, int64_t n, unsigned 
                     if (acc + cnt8[i] >= rem) { b = first - i; break; }
                     if (i < 7) acc += cnt8[i];
                 }
-                if (b < 0) b = 0;
-                s_rem = rem - acc;
-                s_prefix = prefix | ((uint32_t)b << shift);
+                *s_rem = rem - acc;
+                *s_prefix = prefix | ((uint32_t)b << shift);
             }
         }
         __syncthreads();
     }
+    return *s_prefix;
+}
+
+// tau[q] = (a lower bound, good to 16 key bits = 1/128 of its value, of the k-th largest of the n sampled cosines of
+// query q) - band; one CTA per query.
+__global__ void __launch_bounds__(1024)
+cm_kth_kernel(const float *__restrict__ sample, int64_t ld, int64_t n, unsigned k, float band, float *__restrict__ tau, int n_real) {
+    __shared__ unsigned hist[256 * 32];
+    __shared__ uint32_t s_prefix;
+    __shared__ unsigned s_rem;
+    const float *d = sample + (int64_t)blockIdx.x * ld;
+    if ((int)blockIdx.x >= n_real) {                                  // padding up to the UMMA N: nothing is a candidate
+        if (threadIdx.x == 0) tau[blockIdx.x] = __int_as_float(0x7f800000);
+        return;
+    }
+    const uint32_t prefix = block_kth_prefix<2>([d](int64_t i) { return cm::similar_key_of(__ldcg(d + i)); }, n, k, hist, &s_prefix, &s_rem);
     if (threadIdx.x == 0) {
-        const float kth = float_of_key(s_prefix);
+        const float kth = float_of_key(prefix);
         tau[blockIdx.x] = (kth == kth) ? kth - band : -__int_as_float(0x7f800000);    // fewer than k valid cosines: everything passes
     }
 }
@@ -443,18 +440,48 @@ __device__ __forceinline__ float exact_cosine(const float4 *__restrict__ t4, int
     return s / norm;
 }
 
-// Candidates re-scored exactly; blockIdx.y = query, its candidates dealt round-robin to the kRescoreCtas x (512 / LPG)
-// lane groups of the grid's row: keys[q][i] = (~key(cosine), row).
-constexpr int kRescoreCtas = 16, kRescoreThreads = 512;
+// One CTA per query finishes it from its candidates (tf32 cosine, row):
+//   1. a_k = the k-th largest tf32 cosine (to 16 key bits, rounded down).  A true top-k row has an exact cosine of at
+//      least a_k - eps (k rows have tf32 cosines >= a_k), so a tf32 cosine of at least a_k - 2 eps: keep those only
+//   2. the survivors (about k of them) re-scored exactly, sorted (cosine desc, row asc), the best k written out.
+// n_out[q] = k, or -1 when the candidates overflowed kCandCap, fewer than k were collected, or more than kFinishCap
+// survive step 1 (the host then runs the one-query path for q).
+constexpr unsigned kFinishCap = 2048;
 
 template <int LPG, int VPL>
-__global__ void __launch_bounds__(kRescoreThreads)
-cm_rescore_kernel(const float *__restrict__ table, int dim4, const float *__restrict__ mean, const float *__restrict__ norms,
-                  const int32_t *__restrict__ cand, const unsigned *__restrict__ cnt, unsigned long long *__restrict__ keys) {
-    const int q_id = blockIdx.y;
+__global__ void __launch_bounds__(1024)
+cm_finish_kernel(const float *__restrict__ table, int dim4, const float *__restrict__ mean, const float *__restrict__ norms,
+                 const unsigned long long *__restrict__ cand, const unsigned *__restrict__ cnt, unsigned k, float band,
+                 int32_t *__restrict__ rows_out, float *__restrict__ sims_out, int *__restrict__ n_out) {
+    __shared__ __align__(16) unsigned hist[256 * 32];                 // later the sort buffer
+    __shared__ int32_t s_rows[kFinishCap];
+    __shared__ uint32_t s_prefix;
+    __shared__ unsigned s_rem, s_m;
+    unsigned long long *s_keys = reinterpret_cast<unsigned long long *>(hist);
+    static_assert(sizeof(hist) >= kFinishCap * sizeof(unsigned long long), "sort buffer");
+    const int q_id = blockIdx.x;
     const unsigned n = cnt[q_id];
-    constexpr unsigned kGroups = kRescoreThreads / LPG;
-    if (n > kCandCap || blockIdx.x * kGroups >= n) return;
+    if (n > kCandCap || n < k) {
+        if (threadIdx.x == 0) n_out[q_id] = -1;
+        return;
+    }
+    const unsigned long long *c = cand + (size_t)q_id * kCandCap;
+    if (threadIdx.x == 0) s_m = 0u;
+    const uint32_t prefix = block_kth_prefix<2>([c](int64_t i) { return (uint32_t)(__ldcg(c + i) >> 32); }, n, k, hist, &s_prefix, &s_rem);
+    const uint32_t keep = cm::similar_key_of(float_of_key(prefix) - band);
+    for (unsigned i = threadIdx.x; i < n; i += blockDim.x) {
+        const unsigned long long e = __ldcg(c + i);
+        if ((uint32_t)(e >> 32) >= keep) {
+            const unsigned slot = atomicAdd(&s_m, 1u);
+            if (slot < kFinishCap) s_rows[slot] = (int32_t)(e & 0xffffffffull);
+        }
+    }
+    __syncthreads();
+    const unsigned m = s_m;
+    if (m > kFinishCap) {                                            // uniform over the CTA
+        if (threadIdx.x == 0) n_out[q_id] = -1;
+        return;
+    }
     const int lane = threadIdx.x & 31, sub = lane & (LPG - 1);
     const float4 *t4 = reinterpret_cast<const float4 *>(table);
     float4 q[VPL];
@@ -463,38 +490,22 @@ cm_rescore_kernel(const float *__restrict__ table, int dim4, const float *__rest
         const int j = sub + LPG * v;
         q[v] = j < dim4 ? reinterpret_cast<const float4 *>(mean + (size_t)q_id * dim4 * 4)[j] : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    // whole warps stay in the loop (the reduction shuffles): the bound is per warp, the tail lanes score row 0 unused
-    const unsigned warp_first = blockIdx.x * kGroups + (threadIdx.x >> 5) * (32 / LPG);
-    for (unsigned base = warp_first; base < n; base += kRescoreCtas * kGroups) {
+    constexpr unsigned kGroups = 1024 / LPG;
+    for (unsigned base = (threadIdx.x >> 5) * (32 / LPG); base < m; base += kGroups) {   // whole warps (the reduction shuffles)
         const unsigned i = base + (unsigned)(lane / LPG);
-        const bool have = i < n;
-        const int32_t row = have ? cand[(size_t)q_id * kCandCap + i] : 0;
+        const bool have = i < m;
+        const int32_t row = have ? s_rows[i] : 0;
         const float d = exact_cosine<LPG, VPL>(t4, dim4, row, q, sub, norms[row]);
-        if (have && sub == 0) keys[(size_t)q_id * kCandCap + i] = ((unsigned long long)(~cm::similar_key_of(d)) << 32) | (uint32_t)row;
-    }
-}
-
-// One CTA per query: sort its candidates (cosine desc, row asc), write the best k.
-// n_out[q] = k, or -1 when the candidates overflowed kCandCap or fewer than k were collected (the host then
-// runs the one-query path for q).
-__global__ void __launch_bounds__(1024)
-cm_topk_kernel(const unsigned long long *__restrict__ keys, const unsigned *__restrict__ cnt, unsigned k,
-               int32_t *__restrict__ rows_out, float *__restrict__ sims_out, int *__restrict__ n_out) {
-    extern __shared__ unsigned long long s_keys[];                   // up to kCandCap entries
-    const int q_id = blockIdx.x;
-    const unsigned n = cnt[q_id];
-    if (n > kCandCap || n < k) {
-        if (threadIdx.x == 0) n_out[q_id] = -1;
-        return;
+        if (have && sub == 0) s_keys[i] = ((unsigned long long)(~cm::similar_key_of(d)) << 32) | (uint32_t)row;
     }
     unsigned size = 64;
-    while (size < n) size <<= 1;
-    for (unsigned i = threadIdx.x; i < size; i += blockDim.x) s_keys[i] = i < n ? keys[(size_t)q_id * kCandCap + i] : ~0ull;
+    while (size < m) size <<= 1;
+    for (unsigned i = m + threadIdx.x; i < size; i += blockDim.x) s_keys[i] = ~0ull;
     __syncthreads();
     for (unsigned span = 2; span <= size; span <<= 1) {              // bitonic, ascending = best first
         for (unsigned stride = span >> 1; stride > 0; stride >>= 1) {
-            for (unsigned c = threadIdx.x; c < size / 2; c += blockDim.x) {
-                const unsigned lo = 2 * c - (c & (stride - 1));
+            for (unsigned p = threadIdx.x; p < size / 2; p += blockDim.x) {
+                const unsigned lo = 2 * p - (p & (stride - 1));
                 const unsigned hi = lo + stride;
                 const bool up = (lo & span) == 0;
                 const unsigned long long x = s_keys[lo], y = s_keys[hi];
@@ -520,11 +531,8 @@ struct cm_similar_batch {
     float *d_tau = nullptr;              // [kMaxNQ]
     unsigned *d_cnt = nullptr;           // [kMaxNQ]
     unsigned *d_err = nullptr;
-    int32_t *d_cand = nullptr;           // [kMaxNQ][kCandCap]
-    unsigned long long *d_keys = nullptr; // [kMaxNQ][kCandCap] exact (~key, row) of the candidates
+    unsigned long long *d_cand = nullptr; // [kMaxNQ][kCandCap] (key of the tf32 cosine, row)
     float *d_sample = nullptr;           // [kMaxNQ][sample_ld]
-    float *d_padded = nullptr;           // experiment: the table with rows padded to a multiple of 128 bytes
-    int64_t padded_rows = 0;
     size_t sample_floats = 0;
     unsigned char *h_result = nullptr;   // page-locked: rows [kMaxNQ][1024] | sims [kMaxNQ][1024] | n [kMaxNQ] | err
     CUtensorMap map_table;
@@ -555,16 +563,15 @@ EncodeTiledFn encode_tiled() {
 }
 
 // [n_rows][dim] fp32, row-major; boxes of box_rows x 32 floats in the 128-byte swizzle, columns past dim read as zero
-int make_map(CUtensorMap *map, const float *base, int64_t n_rows, int dim, int box_rows, int pitch = 0) {
+int make_map(CUtensorMap *map, const float *base, int64_t n_rows, int dim, int box_rows) {
     EncodeTiledFn fn = encode_tiled();
     if (fn == nullptr) return fail(CM_ERR_CUDA, "the driver does not export cuTensorMapEncodeTiled");
     const cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)n_rows};
-    const cuuint64_t gstride[1] = {(cuuint64_t)(pitch > 0 ? pitch : dim) * sizeof(float)};
+    const cuuint64_t gstride[1] = {(cuuint64_t)dim * sizeof(float)};
     const cuuint32_t box[2] = {(cuuint32_t)kChunkFloats, (cuuint32_t)box_rows};
     const cuuint32_t estride[2] = {1, 1};
-    static const int promo = [] { const char *v = getenv("CM_SIMBATCH_L2PROMO"); return v ? atoi(v) : 3; }();
     const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), gdim, gstride, box, estride,
-                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, (CUtensorMapL2promotion)promo,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(CM_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
     return CM_OK;
@@ -593,8 +600,7 @@ int batch_state(cm_engine *e, cm_similar_state *s, cm_similar_batch **out) {
         if (err == cudaSuccess) err = cudaMalloc(&b->d_cnt, kMaxNQ * sizeof(unsigned));
         if (err == cudaSuccess) err = cudaMalloc(&b->d_err, sizeof(unsigned));
         if (err == cudaSuccess) err = cudaMemset(b->d_err, 0, sizeof(unsigned));
-        if (err == cudaSuccess) err = cudaMalloc(&b->d_cand, (size_t)kMaxNQ * kCandCap * sizeof(int32_t));
-        if (err == cudaSuccess) err = cudaMalloc(&b->d_keys, (size_t)kMaxNQ * kCandCap * sizeof(unsigned long long));
+        if (err == cudaSuccess) err = cudaMalloc(&b->d_cand, (size_t)kMaxNQ * kCandCap * sizeof(unsigned long long));
         if (err == cudaSuccess) err = cudaHostAlloc(&b->h_result, kResultRows * 8 + kMaxNQ * sizeof(int), cudaHostAllocDefault);
         if (err == cudaSuccess) {
             int sms = 0;
@@ -611,9 +617,9 @@ int batch_state(cm_engine *e, cm_similar_state *s, cm_similar_batch **out) {
 }
 
 template <int LPG, int VPL>
-void launch_rescore(cm_engine *e, cm_similar_state *s, cm_similar_batch *b, int n_real) {
-    const dim3 grid(kRescoreCtas, (unsigned)n_real);
-    cm_rescore_kernel<LPG, VPL><<<grid, kRescoreThreads, 0, e->stream>>>(e->d_table, e->dim / 4, b->d_mean, s->d_norms, b->d_cand, b->d_cnt, b->d_keys);
+void launch_finish(cm_engine *e, cm_similar_state *s, cm_similar_batch *b, int n_real, unsigned kk, int32_t *h_rows, float *h_sims, int *h_n) {
+    cm_finish_kernel<LPG, VPL><<<n_real, 1024, 0, e->stream>>>(e->d_table, e->dim / 4, b->d_mean, s->d_norms, b->d_cand, b->d_cnt, kk, kBand,
+                                                               h_rows, h_sims, h_n);
     cm::count_launch();
 }
 
@@ -622,7 +628,7 @@ void launch_rescore(cm_engine *e, cm_similar_state *s, cm_similar_batch *b, int 
 void cm::similar_batch_free(cm_similar_state *s) {
     cm_similar_batch *b = s->batch;
     if (b == nullptr) return;
-    void *ptrs[] = {b->d_mean, b->d_rows, b->d_tau, b->d_cnt, b->d_err, b->d_cand, b->d_keys, b->d_sample, b->d_padded};
+    void *ptrs[] = {b->d_mean, b->d_rows, b->d_tau, b->d_cnt, b->d_err, b->d_cand, b->d_sample};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (b->h_result) cudaFreeHost(b->h_result);
@@ -658,36 +664,18 @@ extern "C" int cm_most_similar_batch(cm_engine *e, const int32_t *rows, int n_qu
     cudaStream_t st = e->stream;
     if (!b->attrs_set) {
         CM_CUDA(cudaFuncSetAttribute(cm_simscan_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLimit));
-        CM_CUDA(cudaFuncSetAttribute(cm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(kCandCap * sizeof(unsigned long long))));
         b->attrs_set = true;
     }
-    static const bool padded = [] { const char *v = getenv("CM_SIMBATCH_PADDED"); return v != nullptr && *v == '1'; }();
-    if (b->map_table_ptr != e->d_table || b->map_table_rows != e->n_rows || (padded && s->batch_table_stale)) {
-        if (padded) {
-            const int pitch = (e->dim + kChunkFloats - 1) / kChunkFloats * kChunkFloats;
-            if (b->padded_rows != e->n_rows) {
-                if (b->d_padded) cudaFree(b->d_padded);
-                b->d_padded = nullptr;
-                b->padded_rows = 0;
-                CM_CUDA(cudaMalloc(&b->d_padded, (size_t)e->n_rows * pitch * sizeof(float)));
-                b->padded_rows = e->n_rows;
-            }
-            cm_pad_rows_kernel<<<148 * 8, 256, 0, st>>>(reinterpret_cast<const float4 *>(e->d_table), e->n_rows, e->dim / 4, pitch / 4,
-                                                       reinterpret_cast<float4 *>(b->d_padded));
-            cm::count_launch();
-            if (int rc = make_map(&b->map_table, b->d_padded, e->n_rows, e->dim, kTileRows, pitch)) return rc;
-            s->batch_table_stale = false;
-        } else if (int rc = make_map(&b->map_table, e->d_table, e->n_rows, e->dim, kTileRows)) {
-            return rc;
-        }
+    if (b->map_table_ptr != e->d_table || b->map_table_rows != e->n_rows) {
+        if (int rc = make_map(&b->map_table, e->d_table, e->n_rows, e->dim, kTileRows)) return rc;
         b->map_table_ptr = e->d_table;
         b->map_table_rows = e->n_rows;
     }
     // the sample: every S-th tile, S chosen so that the k-th largest of the sample admits about k * S candidates
     const int n_tiles = (int)((e->n_rows + kTileRows - 1) / kTileRows);
-    int stride = n_tiles / 512;
-    if (stride > 2048 / (int)kk) stride = 2048 / (int)kk;
-    if (stride > 64) stride = 64;
+    int stride = n_tiles / 256;
+    if (stride > (int)(kCandCap / 4) / (int)kk) stride = (int)(kCandCap / 4) / (int)kk;
+    if (stride > 128) stride = 128;
     if (stride < 1) stride = 1;
     const int n_sample_visits = (n_tiles + stride - 1) / stride;
     const int64_t sample_ld = (int64_t)n_sample_visits * kTileRows;
@@ -741,12 +729,10 @@ extern "C" int cm_most_similar_batch(cm_engine *e, const int32_t *rows, int n_qu
         grid = n_tiles < b->sm_count ? n_tiles : b->sm_count;
         cm_simscan_tc_kernel<<<grid, kScanThreads, smem, st>>>(b->map_table, map_q, a);
         cm::count_launch();
-        if (cm::similar_uses_scan16(dim4)) launch_rescore<16, 5>(e, s, b, n_real);
-        else if (dim4 <= 32) launch_rescore<32, 1>(e, s, b, n_real);
-        else if (dim4 <= 64) launch_rescore<32, 2>(e, s, b, n_real);
-        else launch_rescore<32, 3>(e, s, b, n_real);
-        cm_topk_kernel<<<n_real, 1024, kCandCap * sizeof(unsigned long long), st>>>(b->d_keys, b->d_cnt, kk, h_rows, h_sims, h_n);
-        cm::count_launch();
+        if (cm::similar_uses_scan16(dim4)) launch_finish<16, 5>(e, s, b, n_real, kk, h_rows, h_sims, h_n);
+        else if (dim4 <= 32) launch_finish<32, 1>(e, s, b, n_real, kk, h_rows, h_sims, h_n);
+        else if (dim4 <= 64) launch_finish<32, 2>(e, s, b, n_real, kk, h_rows, h_sims, h_n);
+        else launch_finish<32, 3>(e, s, b, n_real, kk, h_rows, h_sims, h_n);
         CM_CUDA(cudaGetLastError());
         const cudaError_t sync = cudaStreamSynchronize(st);
         if (sync != cudaSuccess)

@@ -24,7 +24,6 @@ struct cm_similar_state {
     unsigned long long *d_cand = nullptr;
     bool norms_ready = false;
     cm_similar_batch *batch = nullptr;   // scratch of cm_most_similar_batch, allocated on first use
-    bool batch_table_stale = true;       // the batched path's derived copy of the table must be rebuilt
 };
 
 namespace cm {
