@@ -11,11 +11,14 @@
 //                          K = 300 in ten 128-byte chunks fed by TMA (SWIZZLE_128B, out-of-range columns
 //                          zero-filled), fp32 accumulators in tensor memory, double-buffered so the epilogue
 //                          of one tile overlaps the MMAs of the next.  One persistent CTA per SM:
-//                          warp 0 = TMA producer, warp 1 = MMA issuer, warps 2-9 = epilogue.
+//                          warp 0 = TMA producer, warp 1 = MMA issuer, warps 2-9 = epilogue.  Above 64 queries
+//                          per pass the two CTAs of an SM pair share 256-row tiles (cta_group::2), each
+//                          holding half of the query block.
 //                          The tf32 cosines are only a FILTER (|error| < 2^-9, see kBand):
 //                            mode 0  sample pass over every S-th tile: approximate cosines written out,
 //                                    cm_kth_kernel takes the k-th largest per query as threshold tau_q
-//                            mode 1  full pass: every (row, q) with cosine >= tau_q - band is a candidate
+//                            mode 1  full pass: every (row, q) with cosine >= tau_q - band is a candidate, appended by
+//                                    the epilogue warp to its own list (cm_bucket_kernel sorts the lists by query)
 //   cm_finish_kernel       per query: candidates cut down to those within the error band of the k-th largest tf32
 //                          cosine, re-scored in fp32 with exactly the arithmetic of the one-query scan (same lanes,
 //                          same FMA order, dot / norm), sorted (cosine desc, row asc), top k out.
@@ -44,10 +47,11 @@ constexpr int kChunkFloats = 32;        // one 128-byte swizzle row of K
 constexpr int kMaxChunks = 10;          // dim <= 320
 constexpr int kMaxStages = 8;           // A ring: up to 8 x 16 KB (what the query block leaves free)
 constexpr int kStageBytes = kTileRows * kChunkFloats * 4;
-constexpr int kMaxNQ = 128;             // queries per pass (UMMA N)
-constexpr int kTmemCols = 256;          // two accumulators of kMaxNQ columns
+constexpr int kMaxNQ = 256;             // queries per pass (UMMA N): 128 on one CTA per SM, 256 on CTA pairs
 constexpr int kScanThreads = 320;        // TMA warp, MMA warp, eight epilogue warps
 constexpr unsigned kCandCap = 16384;    // candidates per query the full pass may collect
+constexpr int kEpilogueWarps = 8;
+constexpr unsigned kEmitCap = 4096;     // (tf32 key, row, query) entries one epilogue warp may emit per pass (64 KB)
 // tf32 keeps 10 mantissa bits (truncation): each product is off by < 2^-9 relative, so a cosine (unit query,
 // division by the row norm) by < 2^-9 absolute.  Threshold and candidate are both approximate: 2 x 2^-9.
 constexpr float kBand = 4.0e-3f;
@@ -127,7 +131,7 @@ enum : unsigned { kErrNone = 0, kErrEmpty = 1, kErrFull = 2, kErrQueries = 3, kE
 struct ScanArgs {
     const float *norms;
     int64_t n_rows;
-    int n_visits;            // tiles this launch visits: tile = tile_first + visit * tile_stride
+    int n_visits;            // tiles (of 128 rows per CTA of the unit) this launch visits: tile = visit * tile_stride
     int tile_stride;
     int nq;                  // UMMA N: queries padded to a multiple of 16, <= kMaxNQ
     int dim;
@@ -136,20 +140,63 @@ struct ScanArgs {
     float *sample_out;       // [nq][sample_ld]
     int64_t sample_ld;
     const float *tau;        // [nq] thresholds, band already subtracted
-    unsigned long long *cand; // [nq][kCandCap]: (key of the tf32 cosine) << 32 | row
-    unsigned *cnt;           // [nq]
+    uint4 *emit;             // [gridDim.x * kEpilogueWarps][kEmitCap]: (key of the tf32 cosine, row, query, 0), per epilogue warp
+    unsigned *emit_cnt;      // [gridDim.x * kEpilogueWarps] entries written (> kEmitCap: the warp overflowed)
     unsigned *err;
 };
 
 // --------------------------------------------------------------------------------------------------
+// CTAS = 1: one CTA per SM, M = 128.  CTAS = 2: the two CTAs of a cluster (one SM pair) work on one tile of 256 rows
+// with tcgen05.mma.cta_group::2 -- each loads its 128 table rows and HALF of the query block (the hardware reads the
+// other half from the partner's shared memory), so the query block costs half the shared memory per SM and the ring
+// is twice as deep at the same number of queries.  Rank 0 issues the MMAs for both; every TMA load of the pair
+// completes on rank 0's barrier (no multicast: each CTA loads its own bytes, all from this GPU's memory), and
+// tcgen05.commit arrives on the same barrier in both CTAs.
+constexpr uint32_t kLeaderMask = 0xFEFFFFFFu;            // shared::cluster address of the same offset in CTA rank 0
+
+template <int CTAS>
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
+    if constexpr (CTAS == 1) {
+        tma_load_2d(dst, map, c0, c1, bar);
+    } else {
+        asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                     :: "r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar & kLeaderMask), "r"(c0), "r"(c1) : "memory");
+    }
+}
+template <int CTAS>
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {
+    if constexpr (CTAS == 1) {
+        tc_commit(bar);
+    } else {
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                     :: "r"(bar), "h"((uint16_t)3) : "memory");
+    }
+}
+template <int CTAS, bool ACC>
+__device__ __forceinline__ void tc_mma_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc) {
+    if constexpr (CTAS == 1) {
+        tc_mma_tf32<ACC>(d_tmem, a_desc, b_desc, idesc);
+    } else {
+        asm volatile("{\n\t.reg .pred p;\n\t"
+                     "setp.ne.b32 p, %4, 0;\n\t"
+                     "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                     :: "r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "n"(ACC ? 1 : 0) : "memory");
+    }
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+template <int CTAS>
 __global__ void __launch_bounds__(kScanThreads, 1)
 cm_simscan_tc_kernel(const __grid_constant__ CUtensorMap map_table, const __grid_constant__ CUtensorMap map_queries,
                      const ScanArgs a) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    // carve: [A ring][queries: n_chunks x nq x 128 B][tau][barriers][tmem ptr]
+    // carve: [A ring][this CTA's share of the queries: n_chunks x nq / CTAS x 128 B][tau][barriers][tmem ptr]
     unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const int n_chunks = (a.dim + kChunkFloats - 1) / kChunkFloats;
-    const uint32_t q_chunk_bytes = (uint32_t)a.nq * 128u;
+    const int nq_local = a.nq / CTAS;
+    const uint32_t q_chunk_bytes = (uint32_t)nq_local * 128u;
     unsigned char *s_a = smem;
     unsigned char *s_q = s_a + a.stages * kStageBytes;
     float *s_tau = reinterpret_cast<float *>(s_q + (size_t)n_chunks * q_chunk_bytes);
@@ -159,46 +206,58 @@ cm_simscan_tc_kernel(const __grid_constant__ CUtensorMap map_table, const __grid
     uint32_t *s_tmem = reinterpret_cast<uint32_t *>(bars + 2 * kMaxStages + 5);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int my_visits = a.n_visits > (int)blockIdx.x ? (a.n_visits - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+    uint32_t rank = 0;
+    if constexpr (CTAS == 2) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    const int unit = (int)blockIdx.x / CTAS, n_units = (int)gridDim.x / CTAS;     // a unit = the CTA(s) sharing tiles
+    const int my_visits = a.n_visits > unit ? (a.n_visits - unit + n_units - 1) / n_units : 0;
+    constexpr int kUnitRows = kTileRows * CTAS;
+    uint32_t tmem_cols = 32;
+    while (tmem_cols < 2u * (uint32_t)a.nq) tmem_cols <<= 1;                      // two accumulators of nq columns
 
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < kMaxStages; ++i) { mbar_init(smem_u32(bar_full + i), 1); mbar_init(smem_u32(bar_empty + i), 1); }
         mbar_init(smem_u32(bar_q), 1);
-        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(bar_tfull + i), 1); mbar_init(smem_u32(bar_tempty + i), 8); }
+        for (int i = 0; i < 2; ++i) { mbar_init(smem_u32(bar_tfull + i), 1); mbar_init(smem_u32(bar_tempty + i), 8 * CTAS); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 2) {                                      // one warp allocates tensor memory (and frees it at the end)
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(s_tmem)), "r"((uint32_t)kTmemCols) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (warp == 2) {                                      // one warp (of each CTA) allocates tensor memory, and frees it at the end
+        if constexpr (CTAS == 1) {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(s_tmem)), "r"(tmem_cols) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_u32(s_tmem)), "r"(tmem_cols) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        }
     }
-    if (threadIdx.x < kMaxNQ) s_tau[threadIdx.x] = (a.mode == 1 && (int)threadIdx.x < a.nq) ? a.tau[threadIdx.x] : 0.f;
+    for (int i = threadIdx.x; i < kMaxNQ; i += kScanThreads) s_tau[i] = (a.mode == 1 && i < a.nq) ? a.tau[i] : 0.f;
     tc_fence_before();
     __syncthreads();
+    if constexpr (CTAS == 2) cluster_sync_all();          // the partner's barriers exist before anything arrives on them
     tc_fence_after();
     const uint32_t tmem_base = *s_tmem;
 
     if (warp == 0) {
-        // ===== TMA producer =====
+        // ===== TMA producer (both CTAs of a pair; rank 0 posts the byte counts for both) =====
         if (lane == 0 && my_visits > 0) {
-            mbar_expect_tx(smem_u32(bar_q), (uint32_t)n_chunks * q_chunk_bytes);
+            if (rank == 0) mbar_expect_tx(smem_u32(bar_q), (uint32_t)n_chunks * q_chunk_bytes * CTAS);
             for (int c = 0; c < n_chunks; ++c)
-                tma_load_2d(smem_u32(s_q) + (uint32_t)c * q_chunk_bytes, &map_queries, c * kChunkFloats, 0, smem_u32(bar_q));
+                tma_load_2d_pair<CTAS>(smem_u32(s_q) + (uint32_t)c * q_chunk_bytes, &map_queries, c * kChunkFloats, (int)rank * nq_local, smem_u32(bar_q));
             uint32_t s = 0, ph = 0;
             for (int v = 0; v < my_visits; ++v) {
-                const int tile = ((int)blockIdx.x + v * (int)gridDim.x) * a.tile_stride;
+                const int row0 = (unit + v * n_units) * a.tile_stride * kUnitRows + (int)rank * kTileRows;
                 for (int c = 0; c < n_chunks; ++c) {
                     mbar_wait(smem_u32(bar_empty + s), ph ^ 1u, a.err, kErrEmpty);
-                    mbar_expect_tx(smem_u32(bar_full + s), kStageBytes);
-                    tma_load_2d(smem_u32(s_a) + s * kStageBytes, &map_table, c * kChunkFloats, tile * kTileRows, smem_u32(bar_full + s));
+                    if (rank == 0) mbar_expect_tx(smem_u32(bar_full + s), kStageBytes * CTAS);
+                    tma_load_2d_pair<CTAS>(smem_u32(s_a) + s * kStageBytes, &map_table, c * kChunkFloats, row0, smem_u32(bar_full + s));
                     if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1u; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (lane == 0 && my_visits > 0) {
-            // instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, tf32 x tf32, both K-major, N, M = 128
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(a.nq >> 3) << 17) | ((uint32_t)(kTileRows >> 4) << 24);
+        // ===== MMA issuer (rank 0 only) =====
+        if (lane == 0 && my_visits > 0 && rank == 0) {
+            // instruction descriptor (cute::UMMA::InstrDescriptor): fp32 accumulate, tf32 x tf32, both K-major, N, M = 128 per CTA
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(a.nq >> 3) << 17) | ((uint32_t)(kUnitRows >> 4) << 24);
             mbar_wait(smem_u32(bar_q), 0, a.err, kErrQueries);
             // The issuing thread is the serial resource of this kernel (one instruction per 8 columns of K): descriptors
             // are running sums, the ring position a counter, the four MMAs of a chunk straight-line code.
@@ -210,48 +269,50 @@ cm_simscan_tc_kernel(const __grid_constant__ CUtensorMap map_table, const __grid
             uint64_t da = da0;
             for (int v = 0; v < my_visits; ++v) {
                 const uint32_t acc = (uint32_t)v & 1u, tph = ((uint32_t)v >> 1) & 1u;
-                mbar_wait(smem_u32(bar_tempty + acc), tph ^ 1u, a.err, kErrTmemEmpty);     // epilogue has drained this accumulator
+                mbar_wait(smem_u32(bar_tempty + acc), tph ^ 1u, a.err, kErrTmemEmpty);     // the epilogues have drained this accumulator
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * (uint32_t)a.nq;
                 uint64_t db = db0;
                 for (int c = 0; c < n_chunks; ++c) {
                     mbar_wait(smem_u32(bar_full + s), ph, a.err, kErrFull);
                     tc_fence_after();
-                    if (c == 0) tc_mma_tf32<false>(d_tmem, da, db, idesc);                    // +32 bytes of K = +2 in the address field
-                    else tc_mma_tf32<true>(d_tmem, da, db, idesc);
+                    if (c == 0) tc_mma_pair<CTAS, false>(d_tmem, da, db, idesc);              // +32 bytes of K = +2 in the address field
+                    else tc_mma_pair<CTAS, true>(d_tmem, da, db, idesc);
                     if (c + 1 < n_chunks || last_steps == 4) {
-                        tc_mma_tf32<true>(d_tmem, da + 2, db + 2, idesc);
-                        tc_mma_tf32<true>(d_tmem, da + 4, db + 4, idesc);
-                        tc_mma_tf32<true>(d_tmem, da + 6, db + 6, idesc);
+                        tc_mma_pair<CTAS, true>(d_tmem, da + 2, db + 2, idesc);
+                        tc_mma_pair<CTAS, true>(d_tmem, da + 4, db + 4, idesc);
+                        tc_mma_pair<CTAS, true>(d_tmem, da + 6, db + 6, idesc);
                     } else {
-                        for (int k = 1; k < last_steps; ++k) tc_mma_tf32<true>(d_tmem, da + 2 * k, db + 2 * k, idesc);
+                        for (int k = 1; k < last_steps; ++k) tc_mma_pair<CTAS, true>(d_tmem, da + 2 * k, db + 2 * k, idesc);
                     }
-                    tc_commit(smem_u32(bar_empty + s));                                       // stage free once these MMAs have read it
+                    tc_commit_pair<CTAS>(smem_u32(bar_empty + s));                            // stage free (in both CTAs) once these MMAs have read it
                     db += db_step;
                     da += da_step;
                     if (++s == (uint32_t)a.stages) { s = 0; ph ^= 1u; da = da0; }
                 }
-                tc_commit(smem_u32(bar_tfull + acc));                                         // accumulator complete
+                tc_commit_pair<CTAS>(smem_u32(bar_tfull + acc));                              // accumulator complete (in both CTAs)
             }
         }
     } else {
-        // ===== epilogue: warps 2..9.  A warp may only read TMEM lanes 32 * (warp % 4) .. + 32 (= tile rows); the two
-        // warps of a quarter split the query columns in blocks of 16 =====
+        // ===== epilogue: warps 2..9.  A warp may only read TMEM lanes 32 * (warp % 4) .. + 32 (= this CTA's tile rows); the
+        // two warps of a quarter split the query columns in blocks of 16 =====
         const int quarter = warp & 3;
         const int half = (warp - 2) >> 2;
-        const int row_in_tile = quarter * 32 + lane;
+        const int row_in_unit = (int)rank * kTileRows + quarter * 32 + lane;
         // this row's norm, fetched two tiles ahead: under the scan's own traffic a load takes about as long as a tile
         auto norm_of = [&](int v) -> float {
             if (v >= my_visits) return 1.f;
-            const int64_t r = (int64_t)((int)blockIdx.x + v * (int)gridDim.x) * a.tile_stride * kTileRows + row_in_tile;
+            const int64_t r = (int64_t)(unit + v * n_units) * a.tile_stride * kUnitRows + row_in_unit;
             return r < a.n_rows ? a.norms[r] : __int_as_float(0x7fc00000);          // rows past the end: NaN, never a candidate
         };
         float nrm0 = norm_of(0), nrm1 = norm_of(1);
+        const size_t emit_id = (size_t)blockIdx.x * kEpilogueWarps + (warp - 2);
+        uint4 *my_emit = a.emit + emit_id * kEmitCap;
+        unsigned cursor = 0;
         for (int v = 0; v < my_visits; ++v) {
-            const int visit = (int)blockIdx.x + v * (int)gridDim.x;
-            const int tile = visit * a.tile_stride;
+            const int visit = unit + v * n_units;
             const uint32_t acc = (uint32_t)v & 1u, tph = ((uint32_t)v >> 1) & 1u;
-            const int64_t row = (int64_t)tile * kTileRows + row_in_tile;
+            const int64_t row = (int64_t)visit * a.tile_stride * kUnitRows + row_in_unit;
             const float nrm2 = norm_of(v + 2);
             const float inv = 1.0f / nrm0;
             nrm0 = nrm1;
@@ -264,7 +325,7 @@ cm_simscan_tc_kernel(const __grid_constant__ CUtensorMap map_table, const __grid
                 __syncwarp();                                    // tcgen05.ld is warp-wide: rejoin after the emit branch
                 tc_ld16(taddr + (uint32_t)c0, d);
                 if (a.mode == 0) {
-                    float *out = a.sample_out + (int64_t)c0 * a.sample_ld + (int64_t)visit * kTileRows + row_in_tile;
+                    float *out = a.sample_out + (int64_t)c0 * a.sample_ld + (int64_t)visit * kUnitRows + row_in_unit;
 #pragma unroll
                     for (int i = 0; i < 16; ++i) out[(int64_t)i * a.sample_ld] = d[i] * inv;
                 } else {
@@ -280,25 +341,38 @@ cm_simscan_tc_kernel(const __grid_constant__ CUtensorMap map_table, const __grid
                         hits |= (d[4 * i + 2] >= t.z ? 1u : 0u) << (4 * i + 2);
                         hits |= (d[4 * i + 3] >= t.w ? 1u : 0u) << (4 * i + 3);
                     }
-                    while (hits != 0u) {
-                        const int i = __ffs(hits) - 1;
+                    // hits are rare (about k * S per query and pass): the warp appends them to its own list, the cursor
+                    // a register -- an atomicAdd whose result is needed would cost a memory round trip per tile
+                    while (__any_sync(cm::kFullMask, hits != 0u)) {
+                        const bool has = hits != 0u;
+                        const unsigned vote = __ballot_sync(cm::kFullMask, has);
+                        const int i = has ? __ffs(hits) - 1 : 0;
                         hits &= hits - 1u;
-                        const unsigned slot = atomicAdd(a.cnt + c0 + i, 1u);
-                        if (slot < kCandCap)
-                            a.cand[(size_t)(c0 + i) * kCandCap + slot] = ((unsigned long long)cm::similar_key_of(d[i]) << 32) | (uint32_t)row;
+                        const unsigned pos = cursor + (unsigned)__popc(vote & ((1u << lane) - 1u));
+                        if (has && pos < kEmitCap)
+                            my_emit[pos] = make_uint4(cm::similar_key_of(d[i]), (uint32_t)row, (uint32_t)(c0 + i), 0u);
+                        cursor += (unsigned)__popc(vote);
                     }
                 }
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(bar_tempty + acc));
+            if (lane == 0) {                                     // the issuer (rank 0) counts the epilogue warps of both CTAs
+                if constexpr (CTAS == 1) mbar_arrive(smem_u32(bar_tempty + acc));
+                // relaxed: what the arrival publishes are TMEM reads, ordered by the tcgen05 fence above -- a release at
+                // cluster scope would also wait for this warp's global stores (18 % of the stall samples of the first version)
+                else asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" :: "r"(smem_u32(bar_tempty + acc) & kLeaderMask) : "memory");
+            }
         }
+        if (a.mode == 1 && lane == 0) a.emit_cnt[emit_id] = cursor;
     }
     tc_fence_before();
     __syncthreads();
+    if constexpr (CTAS == 2) cluster_sync_all();          // neither CTA leaves while the other may still signal it
     if (warp == 2) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"((uint32_t)kTmemCols) : "memory");
+        if constexpr (CTAS == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(tmem_cols) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" :: "r"(tmem_base), "r"(tmem_cols) : "memory");
     }
 }
 
@@ -440,6 +514,33 @@ __device__ __forceinline__ float exact_cosine(const float4 *__restrict__ t4, int
     return s / norm;
 }
 
+// The epilogue warps' lists sorted into per-query candidate lists: one CTA per list.  Counts per query in shared memory,
+// one global atomicAdd per (list, query) reserves the range, a second walk over the list scatters.
+// A list that overflowed poisons every query (cnt = 2^31): the host then runs them one by one.
+__global__ void __launch_bounds__(256)
+cm_bucket_kernel(const uint4 *__restrict__ emit, const unsigned *__restrict__ emit_cnt, int nq,
+                 unsigned long long *__restrict__ cand, unsigned *__restrict__ cnt) {
+    __shared__ unsigned hist[kMaxNQ], cursor[kMaxNQ];
+    const unsigned n_raw = emit_cnt[blockIdx.x];
+    if (n_raw > kEmitCap) {
+        for (int q = threadIdx.x; q < nq; q += blockDim.x) atomicOr(cnt + q, 0x80000000u);
+        return;
+    }
+    if (n_raw == 0) return;
+    const uint4 *list = emit + (size_t)blockIdx.x * kEmitCap;
+    for (int q = threadIdx.x; q < kMaxNQ; q += blockDim.x) hist[q] = 0u;
+    __syncthreads();
+    for (unsigned i = threadIdx.x; i < n_raw; i += blockDim.x) atomicAdd(&hist[list[i].z], 1u);
+    __syncthreads();
+    for (int q = threadIdx.x; q < nq; q += blockDim.x) cursor[q] = hist[q] ? atomicAdd(cnt + q, hist[q]) : 0u;
+    __syncthreads();
+    for (unsigned i = threadIdx.x; i < n_raw; i += blockDim.x) {
+        const uint4 e = list[i];
+        const unsigned pos = atomicAdd(&cursor[e.z], 1u);
+        if (pos < kCandCap) cand[(size_t)e.z * kCandCap + pos] = ((unsigned long long)e.x << 32) | e.y;
+    }
+}
+
 // One CTA per query finishes it from its candidates (tf32 cosine, row):
 //   1. a_k = the k-th largest tf32 cosine (to 16 key bits, rounded down).  A true top-k row has an exact cosine of at
 //      least a_k - eps (k rows have tf32 cosines >= a_k), so a tf32 cosine of at least a_k - 2 eps: keep those only
@@ -532,6 +633,8 @@ struct cm_similar_batch {
     unsigned *d_cnt = nullptr;           // [kMaxNQ]
     unsigned *d_err = nullptr;
     unsigned long long *d_cand = nullptr; // [kMaxNQ][kCandCap] (key of the tf32 cosine, row)
+    uint4 *d_emit = nullptr;             // [sm_count * kEpilogueWarps][kEmitCap] the epilogue warps' own lists
+    unsigned *d_emit_cnt = nullptr;      // [sm_count * kEpilogueWarps]
     float *d_sample = nullptr;           // [kMaxNQ][sample_ld]
     size_t sample_floats = 0;
     unsigned char *h_result = nullptr;   // page-locked: rows [kMaxNQ][1024] | sims [kMaxNQ][1024] | n [kMaxNQ] | err
@@ -606,6 +709,8 @@ int batch_state(cm_engine *e, cm_similar_state *s, cm_similar_batch **out) {
             int sms = 0;
             if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, e->device) == cudaSuccess && sms > 0) b->sm_count = sms;
         }
+        if (err == cudaSuccess) err = cudaMalloc(&b->d_emit, (size_t)b->sm_count * kEpilogueWarps * kEmitCap * sizeof(uint4));
+        if (err == cudaSuccess) err = cudaMalloc(&b->d_emit_cnt, (size_t)b->sm_count * kEpilogueWarps * sizeof(unsigned));
         if (err != cudaSuccess) {
             cudaGetLastError();
             cm::similar_batch_free(s);
@@ -628,7 +733,7 @@ void launch_finish(cm_engine *e, cm_similar_state *s, cm_similar_batch *b, int n
 void cm::similar_batch_free(cm_similar_state *s) {
     cm_similar_batch *b = s->batch;
     if (b == nullptr) return;
-    void *ptrs[] = {b->d_mean, b->d_rows, b->d_tau, b->d_cnt, b->d_err, b->d_cand, b->d_sample};
+    void *ptrs[] = {b->d_mean, b->d_rows, b->d_tau, b->d_cnt, b->d_err, b->d_cand, b->d_emit, b->d_emit_cnt, b->d_sample};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (b->h_result) cudaFreeHost(b->h_result);
@@ -663,42 +768,52 @@ extern "C" int cm_most_similar_batch(cm_engine *e, const int32_t *rows, int n_qu
     if (int rc = batch_state(e, s, &b)) return rc;
     cudaStream_t st = e->stream;
     if (!b->attrs_set) {
-        CM_CUDA(cudaFuncSetAttribute(cm_simscan_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLimit));
+        CM_CUDA(cudaFuncSetAttribute(cm_simscan_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLimit));
+        CM_CUDA(cudaFuncSetAttribute(cm_simscan_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLimit));
         b->attrs_set = true;
     }
+    // CTA pairs (tcgen05 cta_group::2) for passes of more than 64 queries: half the query block per SM, so the ring stays
+    // eight deep up to 128 queries (684 against 744 us per pass) and 256 queries fit at all.  CM_SIMILAR_PAIR=0|1 forces it.
+    static const int pair_forced = [] { const char *v = getenv("CM_SIMILAR_PAIR"); return v != nullptr && *v != 0 ? atoi(v) : -1; }();
     if (b->map_table_ptr != e->d_table || b->map_table_rows != e->n_rows) {
         if (int rc = make_map(&b->map_table, e->d_table, e->n_rows, e->dim, kTileRows)) return rc;
         b->map_table_ptr = e->d_table;
         b->map_table_rows = e->n_rows;
     }
-    // the sample: every S-th tile, S chosen so that the k-th largest of the sample admits about k * S candidates
-    const int n_tiles = (int)((e->n_rows + kTileRows - 1) / kTileRows);
-    int stride = n_tiles / 256;
-    if (stride > (int)(kCandCap / 4) / (int)kk) stride = (int)(kCandCap / 4) / (int)kk;
-    if (stride > 128) stride = 128;
-    if (stride < 1) stride = 1;
-    const int n_sample_visits = (n_tiles + stride - 1) / stride;
-    const int64_t sample_ld = (int64_t)n_sample_visits * kTileRows;
-    if (b->sample_floats < (size_t)sample_ld * kMaxNQ) {
-        if (b->d_sample) cudaFree(b->d_sample);
-        b->d_sample = nullptr;
-        b->sample_floats = 0;
-        CM_CUDA(cudaMalloc(&b->d_sample, (size_t)sample_ld * kMaxNQ * sizeof(float)));
-        b->sample_floats = (size_t)sample_ld * kMaxNQ;
-    }
     int32_t *h_rows = reinterpret_cast<int32_t *>(b->h_result);
     float *h_sims = reinterpret_cast<float *>(b->h_result + kResultRows * 4);
     int *h_n = reinterpret_cast<int *>(b->h_result + kResultRows * 8);
     const int dim4 = e->dim / 4;
-    for (int q0 = 0; q0 < n_queries; q0 += kMaxNQ) {
-        const int n_real = n_queries - q0 < kMaxNQ ? n_queries - q0 : kMaxNQ;
+    const int pass_max = pair_forced == 0 ? kMaxNQ / 2 : kMaxNQ;
+    for (int q0 = 0; q0 < n_queries; q0 += pass_max) {
+        const int n_real = n_queries - q0 < pass_max ? n_queries - q0 : pass_max;
         const int nq = (n_real + 15) / 16 * 16;
+        const bool pair = pair_forced >= 0 ? pair_forced != 0 : nq > 64;
+        const int ctas = pair ? 2 : 1;
+        // tiles of 128 rows per CTA of a unit (a CTA, or a CTA pair); the sample is every S-th tile, S chosen so that
+        // about 33,000 rows are sampled and the k-th largest of the sample admits about k * S candidates
+        const int unit_rows = kTileRows * ctas;
+        const int n_tiles = (int)((e->n_rows + unit_rows - 1) / unit_rows);
+        int stride = n_tiles / (256 / ctas);
+        if (stride > (int)(kCandCap / 4) / (int)kk) stride = (int)(kCandCap / 4) / (int)kk;
+        if (stride > 128) stride = 128;
+        if (stride < 1) stride = 1;
+        const int n_sample_visits = (n_tiles + stride - 1) / stride;
+        const int64_t sample_ld = (int64_t)n_sample_visits * unit_rows;
+        if (b->sample_floats < (size_t)sample_ld * kMaxNQ) {
+            CM_CUDA(cudaStreamSynchronize(st));
+            if (b->d_sample) cudaFree(b->d_sample);
+            b->d_sample = nullptr;
+            b->sample_floats = 0;
+            CM_CUDA(cudaMalloc(&b->d_sample, (size_t)sample_ld * kMaxNQ * sizeof(float)));
+            b->sample_floats = (size_t)sample_ld * kMaxNQ;
+        }
         CM_CUDA(cudaMemcpyAsync(b->d_rows, rows + q0, n_real * sizeof(int32_t), cudaMemcpyHostToDevice, st));
         CM_CUDA(cudaMemsetAsync(b->d_cnt, 0, kMaxNQ * sizeof(unsigned), st));
         cm_query_batch_kernel<<<nq, 32, 0, st>>>(e->d_table, e->dim, b->d_rows, n_real, s->d_norms, b->d_mean);
         cm::count_launch();
         CUtensorMap map_q;
-        if (int rc = make_map(&map_q, b->d_mean, nq, e->dim, nq)) return rc;
+        if (int rc = make_map(&map_q, b->d_mean, nq, e->dim, nq / ctas)) return rc;      // a CTA of a pair loads its half of the block
         ScanArgs a = {};
         a.norms = s->d_norms;
         a.n_rows = e->n_rows;
@@ -707,27 +822,44 @@ extern "C" int cm_most_similar_batch(cm_engine *e, const int32_t *rows, int n_qu
         a.sample_out = b->d_sample;
         a.sample_ld = sample_ld;
         a.tau = b->d_tau;
-        a.cand = b->d_cand;
-        a.cnt = b->d_cnt;
+        a.emit = b->d_emit;
+        a.emit_cnt = b->d_emit_cnt;
         a.err = b->d_err;
         const int n_chunks = (e->dim + kChunkFloats - 1) / kChunkFloats;
-        a.stages = scan_stages(nq, n_chunks);
-        const size_t smem = scan_smem(nq, n_chunks, a.stages);
+        a.stages = scan_stages(nq / ctas, n_chunks);
+        const size_t smem = scan_smem(nq / ctas, n_chunks, a.stages);
+        auto launch_scan = [&](int n_units_to_visit) {
+            int grid = b->sm_count / ctas < n_units_to_visit ? b->sm_count / ctas : n_units_to_visit;      // units: CTAs or CTA pairs
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned)(grid * ctas));
+            cfg.blockDim = dim3(kScanThreads);
+            cfg.dynamicSmemBytes = smem;
+            cfg.stream = st;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = (unsigned)ctas;
+            attr[0].val.clusterDim.y = 1;
+            attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            if (pair) cudaLaunchKernelEx(&cfg, cm_simscan_tc_kernel<2>, b->map_table, map_q, a);
+            else cudaLaunchKernelEx(&cfg, cm_simscan_tc_kernel<1>, b->map_table, map_q, a);
+            cm::count_launch();
+            return grid * ctas;
+        };
         // sample pass
         a.mode = 0;
         a.n_visits = n_sample_visits;
         a.tile_stride = stride;
-        int grid = n_sample_visits < b->sm_count ? n_sample_visits : b->sm_count;
-        cm_simscan_tc_kernel<<<grid, kScanThreads, smem, st>>>(b->map_table, map_q, a);
-        cm::count_launch();
+        launch_scan(a.n_visits);
         cm_kth_kernel<<<nq, 1024, 0, st>>>(b->d_sample, sample_ld, sample_ld, kk, kBand, b->d_tau, n_real);
         cm::count_launch();
         // full pass
         a.mode = 1;
         a.n_visits = n_tiles;
         a.tile_stride = 1;
-        grid = n_tiles < b->sm_count ? n_tiles : b->sm_count;
-        cm_simscan_tc_kernel<<<grid, kScanThreads, smem, st>>>(b->map_table, map_q, a);
+        const int scan_ctas = launch_scan(a.n_visits);
+        cm_bucket_kernel<<<scan_ctas * kEpilogueWarps, 256, 0, st>>>(b->d_emit, b->d_emit_cnt, nq, b->d_cand, b->d_cnt);
         cm::count_launch();
         if (cm::similar_uses_scan16(dim4)) launch_finish<16, 5>(e, s, b, n_real, kk, h_rows, h_sims, h_n);
         else if (dim4 <= 32) launch_finish<32, 1>(e, s, b, n_real, kk, h_rows, h_sims, h_n);

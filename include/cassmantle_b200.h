@@ -246,7 +246,7 @@ int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_out, float *
  * reference calls most_similar once per word).  rows[q] is query q's table row; its k best land in
  * rows_out / sims_out [q * k .. q * k + n_out[q]), exactly what cm_most_similar(rows[q], k) returns --
  * the same rows and the same fp32 cosines (entries tied at the k-th place may resolve differently).
- * Up to 64 queries share a pass: the table is multiplied with the query block on the tensor cores in
+ * Up to 256 queries share a pass: the table is multiplied with the query block on the tensor cores in
  * tf32 only to FILTER candidates (threshold from a sampled pass, widened by the tf32 error bound), and
  * the candidates are re-scored with the one-query arithmetic.  Tables wider than 320 columns, a single
  * query, or CM_SIMILAR_BATCH=0 in the environment take the one-query path in a loop.  Host pointers,
