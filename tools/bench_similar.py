@@ -19,7 +19,7 @@ print(f"GPU: p50 {ts[len(ts)//2]:.0f} us per query (topn 50), {bytes_scan / ts[l
 import os
 # many queries per pass (cm_most_similar_batch): tensor-core filter + exact re-score
 rng = np.random.default_rng(1)
-for n_q in (2, 8, 16, 32, 64, 128, 256, 512):
+for n_q in [int(x) for x in os.environ.get('BATCH_SIZES', '2,8,16,32,64,128,256,512').split(',')]:
     queries = rng.integers(0, V, size=n_q).astype(np.int32)
     eng.most_similar_batch(queries, 51)
     reps = []
