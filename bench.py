@@ -1055,7 +1055,7 @@ def run_own(args) -> None:
         got = eng.most_similar_batch(queries, 51)
         tsb = []
         for _ in range(5):
-            t1 = time.perf_counter(); got = eng.most_similar_batch(queries, 51); tsb.append(time.perf_counter() - t1)
+            t1 = time.perf_counter(); got_arrays = eng.most_similar_batch_arrays(queries, 51); tsb.append(time.perf_counter() - t1)
         same = True
         for q, (rows_b, sims_b) in list(zip(queries, got))[:8]:
             rows_1, sims_1 = eng.most_similar(int(q), 51)

@@ -146,16 +146,24 @@ class ScoringEngine:
                                         ctypes.byref(n)))
         return rows[: n.value], sims[: n.value]
 
-    def most_similar_batch(self, rows, k: int):
+    def most_similar_batch_arrays(self, rows, k: int):
         """``most_similar(row, k)`` for every row of ``rows`` in one pass over the table (C ABI
-        cm_most_similar_batch): a list of (rows, sims) pairs, identical to the one-query results."""
+        cm_most_similar_batch): (rows[Q, k], sims[Q, k], n[Q]) -- query q's results are the first n[q] entries of row q,
+        identical to the one-query results."""
         q = np.ascontiguousarray(rows, dtype=np.int32).reshape(-1)
         out_rows = np.empty((q.size, k), dtype=np.int32)
         out_sims = np.empty((q.size, k), dtype=np.float32)
         n = np.zeros(q.size, dtype=np.int32)
         check(self._lib.cm_most_similar_batch(self._h, q.ctypes.data, int(q.size), int(k), out_rows.ctypes.data,
                                               out_sims.ctypes.data, n.ctypes.data))
-        return [(out_rows[i, : n[i]].copy(), out_sims[i, : n[i]].copy()) for i in range(q.size)]
+        return out_rows, out_sims, n
+
+    def most_similar_batch(self, rows, k: int):
+        """The same as a list of (rows, sims) pairs, one per query (views of the two result arrays)."""
+        out_rows, out_sims, n = self.most_similar_batch_arrays(rows, k)
+        if k > 0 and bool((n == k).all()):
+            return list(zip(out_rows, out_sims))
+        return [(out_rows[i, : n[i]], out_sims[i, : n[i]]) for i in range(len(n))]
 
     def score_device(self, d_guess_idx: int, d_guess_len: int, n_guesses: int, n_slots: int,
                      d_answer_slot: int, d_exact: int, min_score: float, d_scores: int,

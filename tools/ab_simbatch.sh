@@ -1,5 +1,5 @@
 #!/bin/bash
+# Developer run: batched most_similar -- tests and timing.
 OUT=gpurun_out; mkdir -p $OUT; TAG=${1:-sb}
-for pm in 160 192 224 256; do
-CM_SIMILAR_PASS_MAX=$pm BATCH_SIZES=$pm,$((2*pm)) NO_CPU=1 timeout 300 python tools/bench_similar.py > $OUT/${TAG}_bench_pm$pm.log 2>&1; echo "pass_max=$pm rc=$?"; grep "queries" $OUT/${TAG}_bench_pm$pm.log
-done
+timeout 300 python -m pytest tests/test_gpu_similar.py -m gpu -x -q > $OUT/${TAG}_tests.log 2>&1; echo "similar tests rc=$?"; tail -2 $OUT/${TAG}_tests.log
+CHECK_BATCH=1 NO_CPU=1 timeout 300 python tools/bench_similar.py > $OUT/${TAG}_bench.log 2>&1; echo "bench rc=$?"; grep "queries\|identical\|p50" $OUT/${TAG}_bench.log

@@ -24,7 +24,7 @@ for n_q in [int(x) for x in os.environ.get('BATCH_SIZES', '2,8,16,32,64,128,256,
     eng.most_similar_batch(queries, 51)
     reps = []
     for _ in range(5):
-        t0 = time.perf_counter(); got = eng.most_similar_batch(queries, 51); reps.append(time.perf_counter() - t0)
+        t0 = time.perf_counter(); got = eng.most_similar_batch_arrays(queries, 51); reps.append(time.perf_counter() - t0)
     t = np.sort(reps)[len(reps) // 2] * 1e6
     print(f"GPU batch: {n_q:4d} queries {t:9.0f} us per call = {t / n_q:7.1f} us per query (topn 50)", flush=True)
 if os.environ.get('CHECK_BATCH'):
