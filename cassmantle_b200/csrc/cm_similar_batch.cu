@@ -758,7 +758,8 @@ extern "C" int cm_most_similar_batch(cm_engine *e, const int32_t *rows, int n_qu
     const unsigned kk = (unsigned)((int64_t)k < e->n_rows ? k : e->n_rows);
     // Test hook / escape hatch: CM_SIMILAR_BATCH=0 runs the queries one by one.
     static const bool batch_off = [] { const char *v = getenv("CM_SIMILAR_BATCH"); return v != nullptr && *v == '0'; }();
-    const bool tensor_path = !batch_off && n_queries >= 2 && e->dim % 4 == 0 && e->dim >= kChunkFloats && e->dim <= kMaxChunks * kChunkFloats;
+    const bool tensor_path = !batch_off && n_queries >= 2 && e->dim % 4 == 0 && e->dim >= kChunkFloats && e->dim <= kMaxChunks * kChunkFloats &&
+                             e->n_rows >= 2 * kTileRows;              // a TMA box is not larger than the table
     if (!tensor_path) {
         for (int q = 0; q < n_queries; ++q)
             if (int rc = cm::most_similar_locked(e, rows[q], k, rows_out + (size_t)q * k, sims_out + (size_t)q * k, n_out + q)) return rc;

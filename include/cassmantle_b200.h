@@ -248,8 +248,9 @@ int cm_most_similar(cm_engine *e, int32_t row, int k, int32_t *rows_out, float *
  * the same rows and the same fp32 cosines (entries tied at the k-th place may resolve differently).
  * Up to 256 queries share a pass: the table is multiplied with the query block on the tensor cores in
  * tf32 only to FILTER candidates (threshold from a sampled pass, widened by the tf32 error bound), and
- * the candidates are re-scored with the one-query arithmetic.  Tables wider than 320 columns, a single
- * query, or CM_SIMILAR_BATCH=0 in the environment take the one-query path in a loop.  Host pointers,
+ * the candidates are re-scored with the one-query arithmetic.  Tables narrower than 32 or wider than 320
+ * columns or shorter than 256 rows, a single query, or CM_SIMILAR_BATCH=0 in the environment take the
+ * one-query path in a loop.  Host pointers,
  * blocking.                                                                                      */
 int cm_most_similar_batch(cm_engine *e, const int32_t *rows, int n_queries, int k,
                           int32_t *rows_out, float *sims_out, int *n_out);

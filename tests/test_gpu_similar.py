@@ -212,7 +212,7 @@ def test_batch_matches_oracle(small_engine, small_table):
 def test_batch_other_widths_and_small_tables():
     from cassmantle_b200.engine import ScoringEngine
     rng = np.random.default_rng(11)
-    for n_rows, dim in ((300, 300), (5000, 64), (4097, 128), (2000, 200), (1500, 320), (900, 324)):
+    for n_rows, dim in ((300, 300), (5000, 64), (4097, 128), (2000, 200), (1500, 320), (900, 324), (40, 300), (500, 16)):
         vec = rng.standard_normal((n_rows, dim)).astype(np.float32)
         vec[7] = vec[3]                                              # a duplicated row: an exact tie
         with ScoringEngine.from_vectors(vec) as eng:
