@@ -64,6 +64,7 @@ bool is_pinned_host(const void *p);
 int check_engine(const cm_engine *e);
 
 void similar_state_free(cm_engine *e);     // cm_similar.cu
+void similar_reserve(cm_engine *e);        // cm_similar.cu: allocate cm_most_similar's scratch now (best effort)
 int ensure_stage(cm_engine *e, size_t bytes);   // e->h_stage holds at least `bytes` (call with e->mu held)
 void similar_invalidate(cm_engine *e);     // the table changed: cached row norms are stale
 void resident_stop(cm_engine *e);          // stop the resident kernel if it runs (it is re-launched on demand)

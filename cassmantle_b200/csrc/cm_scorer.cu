@@ -949,6 +949,7 @@ int cm_engine_create(cm_engine **out, int device, int64_t n_rows, int dim) {
         cm_engine_destroy(e);
         return code;
     }
+    cm::similar_reserve(e);
     *out = e;
     return CM_OK;
 }

@@ -516,6 +516,15 @@ static bool generic_scan_forced() {
     return v;
 }
 
+// Called by cm_engine_create right after the table is allocated.  Where the 12 MB of distances and norms land matters:
+// allocated late in a process's life (after pipes, pinned blocks, other libraries' pools) the same scan has been measured
+// at 650-870 us per query instead of 575 (tools/probe_similar_alloc_order.py, bench.py before this call existed).
+// Failure is not an error here: cm_most_similar allocates on first use as before.
+void cm::similar_reserve(cm_engine *e) {
+    cm_similar_state *s = nullptr;
+    if (similar_state(e, &s) != CM_OK) cudaGetLastError();
+}
+
 bool cm::similar_uses_scan16(int dim4) { return !generic_scan_forced() && dim4 > 64 && dim4 <= 80; }
 
 int cm::similar_prepare(cm_engine *e, cm_similar_state **out) {
