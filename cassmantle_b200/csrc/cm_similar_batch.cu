@@ -767,6 +767,9 @@ extern "C" int cm_most_similar_batch(cm_engine *e, const int32_t *rows, int n_qu
     }
     cm_similar_batch *b = nullptr;
     if (int rc = batch_state(e, s, &b)) return rc;
+    // The scan wants all of an SM's shared memory: beside a CTA of the resident micro-batch kernel (cm_engine_arm_resident)
+    // it would never be scheduled.  That kernel is stopped here and comes back with the next blocking score call.
+    cm::resident_stop(e);
     cudaStream_t st = e->stream;
     if (!b->attrs_set) {
         CM_CUDA(cudaFuncSetAttribute(cm_simscan_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemLimit));

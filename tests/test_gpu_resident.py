@@ -120,3 +120,27 @@ def test_resident_calls_from_several_threads_and_clean_shutdown():
     t0 = time.perf_counter()
     eng.close()                                                                # stops the resident kernel at once
     assert time.perf_counter() - t0 < 0.04
+
+
+def test_batched_most_similar_beside_the_resident_kernel():
+    """The tensor-core scan of cm_most_similar_batch takes all of an SM's shared memory, so it cannot share SMs with
+    the resident kernel: the call stops that kernel (it never idles out here: idle_ms = 0) and the next blocking score
+    call brings it back -- no hang, same results on both sides."""
+    from cassmantle_b200.engine import ScoringEngine
+    with ScoringEngine.synthetic(V, 300, seed=0, device=0) as eng:
+        idx, ln, ans, slot, ex = synth.make_guess_batch(256, 4, V, 2, seed=77, ragged=True)
+        eng.set_answers(ans)
+        want, _ = eng.score_host(idx, ln, slot, ex, 0.01)
+        queries = np.array([5, 1234, 49_999, 17], dtype=np.int32)
+        want_sim = [eng.most_similar(int(q), 11) for q in queries]
+        eng.arm_resident(idle_ms=0)
+        for _ in range(3):
+            got, _ = eng.score_host(idx, ln, slot, ex, 0.01)              # resident path
+            assert np.array_equal(got, want)
+            t0 = time.perf_counter()
+            batch = eng.most_similar_batch(queries, 11)
+            assert time.perf_counter() - t0 < 2.0
+            for (rows, sims), (wr, ws) in zip(batch, want_sim):
+                assert np.array_equal(sims, ws) and np.array_equal(rows, wr)
+        got, _ = eng.score_host(idx, ln, slot, ex, 0.01)
+        assert np.array_equal(got, want)
