@@ -24,6 +24,7 @@
 #include <cuda_runtime.h>
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <algorithm>
 #include <new>
@@ -67,6 +68,143 @@ BoxParams box_params(float gaussian_radius) {
     p.ww = (uint32_t)q;
     p.fw = ((1u << 24) - (uint32_t)(p.radius * 2 + 1) * p.ww) / 2u;
     return p;
+}
+
+// ---- the same three passes on a PLANAR copy of the line (round 2, late) ---------------------------------
+// The interleaved form below spends about ten shared-memory accesses per output byte and pass (byte loads of
+// pixels, two prefix sums, two far pixels, two edge pixels).  Here the line is de-interleaved into one plane per
+// channel, padded on both sides with kPad copies of the edge pixel -- so Pillow's index clamping and its
+// n_left / n_right edge terms become ordinary window sums -- and a thread produces FOUR consecutive bytes of a plane:
+//   the window sum of the first of them is (2r + 1) / 4 word loads added up with __vsadu4 (no prefix sums: a
+//   block-wide scan costs more instructions per pass than it saves, and two barriers),
+//   the two far pixels of the four outputs are two unaligned words (two aligned loads + a funnel shift each),
+//   and the window sum slides from one output to the next with the bytes of those same two words.  Integer arithmetic and rounding are those of the
+// interleaved form (uint32 wrap included): the output is the same, byte for byte.  Needs n % 4 == 0 and
+// radius <= kPad - 2 (the game's blur <= 15 gives a box radius <= 15); other lines take the interleaved form.
+constexpr int kPad = 64;
+
+template <int C>
+__device__ __forceinline__ void box3_planar(const uint8_t *__restrict__ in, uint8_t *__restrict__ out, int n,
+                                            const BoxParams &bp, int passes, uint32_t *smem32) {
+    const int t = threadIdx.x;
+    const int W = n + 2 * kPad, W4 = W >> 2, n4 = n >> 2;
+    uint32_t *cur = smem32;                                // [C][W4] the padded planes
+    uint32_t *nxt = cur + C * W4;
+    const int bytes = n * C;
+    const bool rgb_words = C == 3 && ((((uintptr_t)in) | ((uintptr_t)out)) & 3) == 0;
+    if (rgb_words) {   // four RGB pixels = three words in, one word per plane out: six byte permutes
+        for (int q = t; q < n4; q += 256) {
+            const uint32_t *w = reinterpret_cast<const uint32_t *>(in) + 3 * q;
+            const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];         // R0 G0 B0 R1 | G1 B1 R2 G2 | B2 R3 G3 B3
+            const int at = (kPad >> 2) + q;
+            cur[0 * W4 + at] = __byte_perm(__byte_perm(w0, w1, 0x0630), w2, 0x5210);
+            cur[1 * W4 + at] = __byte_perm(__byte_perm(w0, w1, 0x0741), w2, 0x6210);
+            cur[2 * W4 + at] = __byte_perm(__byte_perm(w0, w1, 0x0052), w2, 0x7410);
+        }
+    } else {   // load and de-interleave byte by byte
+        uint8_t *c8 = reinterpret_cast<uint8_t *>(cur);
+        int done = 0;
+        if (((uintptr_t)in & 15) == 0) {
+            const int n16 = bytes >> 4;
+            for (int v = t; v < n16; v += 256) {
+                const uint4 q = reinterpret_cast<const uint4 *>(in)[v];
+                const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    const int idx = 16 * v + k;
+                    c8[(idx % C) * W + kPad + idx / C] = (uint8_t)(w[k >> 2] >> (8 * (k & 3)));
+                }
+            }
+            done = n16 << 4;
+        }
+        for (int idx = done + t; idx < bytes; idx += 256) c8[(idx % C) * W + kPad + idx / C] = in[idx];
+    }
+    __syncthreads();
+    const int r = bp.radius;
+    constexpr int kPad4 = kPad >> 2;
+    for (int pass = 0; pass < passes; ++pass) {
+        // pads: kPad copies of the first and of the last pixel of every plane
+        if (t < 2 * kPad4) {
+#pragma unroll
+            for (int c = 0; c < C; ++c) {
+                const uint8_t *c8 = reinterpret_cast<const uint8_t *>(cur + c * W4);
+                if (t < kPad4) cur[c * W4 + t] = 0x01010101u * c8[kPad];
+                else cur[c * W4 + kPad4 + n4 + (t - kPad4)] = 0x01010101u * c8[kPad + n - 1];
+            }
+        }
+        __syncthreads();
+        // four consecutive output bytes of one plane per step
+#pragma unroll
+        for (int c = 0; c < C; ++c) {
+            const uint32_t *pw = cur + c * W4;
+            for (int q = t; q < n4; q += 256) {
+                const int p = kPad + 4 * q;                          // padded position of the first output byte
+                const int ihi = p + r + 1, ilo = p - r;              // window [ilo, ihi) of the first output
+                const int first = ilo >> 2, last = ihi >> 2;
+                const int sh_hi = (ihi & 3) * 8, sh_lo = (ilo & 3) * 8;
+                const uint32_t whi = pw[last], wlo = pw[first];
+                // window sum = whole words [first, last) + the bytes of word `last` below ihi - the bytes of word `first`
+                // below ilo.  A block-wide prefix sum would make this two lookups, but building it costs more
+                // instructions per pass than these (2r + 1) / 4 adds (measured: 370 against 250 for the outputs themselves).
+                uint32_t acc = __vsadu4(sh_hi ? (whi << (32 - sh_hi)) : 0u, 0u) - __vsadu4(sh_lo ? (wlo << (32 - sh_lo)) : 0u, 0u);
+                for (int j = first; j < last; ++j) acc += __vsadu4(pw[j], 0u);
+                // bytes [ilo - 1, ilo + 3) and [ihi, ihi + 4): far pixels of the four outputs, and what the window gains / loses
+                const int il = ilo - 1;
+                const uint32_t left4 = __funnelshift_r(pw[il >> 2], pw[(il >> 2) + 1], (il & 3) * 8);
+                const uint32_t right4 = __funnelshift_r(whi, pw[last + 1], sh_hi);
+                uint32_t packed = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t fl = (left4 >> (8 * k)) & 0xffu, fr = (right4 >> (8 * k)) & 0xffu;
+                    const uint32_t bulk = acc * bp.ww + (fl + fr) * bp.fw;
+                    packed |= ((bulk + (1u << 23)) >> 24) << (8 * k);
+                    if (k < 3) acc += fr - ((left4 >> (8 * (k + 1))) & 0xffu);
+                }
+                nxt[c * W4 + (p >> 2)] = packed;
+            }
+        }
+        __syncthreads();
+        uint32_t *tmp = cur; cur = nxt; nxt = tmp;
+    }
+    if (rgb_words) {
+        for (int q = t; q < n4; q += 256) {
+            const int at = (kPad >> 2) + q;
+            const uint32_t R = cur[0 * W4 + at], G = cur[1 * W4 + at], B = cur[2 * W4 + at];
+            uint32_t *w = reinterpret_cast<uint32_t *>(out) + 3 * q;
+            w[0] = __byte_perm(__byte_perm(R, G, 0x1040), B, 0x3410);
+            w[1] = __byte_perm(__byte_perm(G, R, 0x2601), B, 0x3250);
+            w[2] = __byte_perm(__byte_perm(R, G, 0x0730), B, 0x7216);
+        }
+    } else {   // interleave and store
+        const uint8_t *c8 = reinterpret_cast<const uint8_t *>(cur);
+        int done = 0;
+        if (((uintptr_t)out & 15) == 0) {
+            const int n16 = bytes >> 4;
+            for (int v = t; v < n16; v += 256) {
+                uint32_t w[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    const int idx = 16 * v + k;
+                    w[k >> 2] |= (uint32_t)c8[(idx % C) * W + kPad + idx / C] << (8 * (k & 3));
+                }
+                reinterpret_cast<uint4 *>(out)[v] = make_uint4(w[0], w[1], w[2], w[3]);
+            }
+            done = n16 << 4;
+        }
+        for (int idx = done + t; idx < bytes; idx += 256) out[idx] = c8[(idx % C) * W + kPad + idx / C];
+    }
+}
+
+template <int C>
+__global__ void __launch_bounds__(256, 8)
+cm_boxblur3_planar_kernel(const uint8_t *__restrict__ src, size_t src_req_stride, uint8_t *__restrict__ dst,
+                          size_t dst_req_stride, int n, size_t line_stride, const BoxParams *__restrict__ params,
+                          int passes) {
+    extern __shared__ uint32_t smem[];
+    const BoxParams bp = params[blockIdx.y];
+    const uint8_t *in = src + blockIdx.y * src_req_stride + blockIdx.x * line_stride;
+    uint8_t *out = dst + blockIdx.y * dst_req_stride + blockIdx.x * line_stride;
+    box3_planar<C>(in, out, n, bp, bp.identity ? 0 : passes, smem);       // GaussianBlur(0): de-interleave, re-interleave
 }
 
 // The three box-blur passes of one axis along a "line" of `n` pixels of C channels, in ONE kernel: the
@@ -176,11 +314,22 @@ int launch_pass(cm_blur *b, const uint8_t *src, size_t src_req_stride, uint8_t *
                 int n_lines, int n, size_t line_stride, int batch, const void *params) {
     const size_t line = ((size_t)n * C + 15) & ~(size_t)15;
     const size_t smem = (((size_t)C * (n + 1) * sizeof(uint32_t) + 15) & ~(size_t)15) + 2 * line;
-    // per device and cheap: set it on every launch rather than cache a process-wide flag
-    if (smem > 48 * 1024)
-        CM_CUDA(cudaFuncSetAttribute(cm_boxblur3_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    cm_boxblur3_kernel<C><<<dim3((unsigned)n_lines, (unsigned)batch), 256, smem, b->stream>>>(
-        src, src_req_stride, dst, dst_req_stride, n, line_stride, (const BoxParams *)params, 3);
+    // Test hook: CM_BLUR_PLANAR=0 keeps every line on the interleaved form so the two can be compared.
+    static const bool planar_on = [] { const char *v = getenv("CM_BLUR_PLANAR"); return !(v != nullptr && *v == '0'); }();
+    const dim3 grid((unsigned)n_lines, (unsigned)batch);
+    if (planar_on && n >= 4 && (n & 3) == 0 && b->max_box_radius <= kPad - 2) {
+        const size_t smem_planar = 2 * (size_t)C * ((size_t)n + 2 * kPad);
+        if (smem_planar > 48 * 1024)
+            CM_CUDA(cudaFuncSetAttribute(cm_boxblur3_planar_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_planar));
+        cm_boxblur3_planar_kernel<C><<<grid, 256, smem_planar, b->stream>>>(
+            src, src_req_stride, dst, dst_req_stride, n, line_stride, (const BoxParams *)params, 3);
+    } else {
+        // per device and cheap: set it on every launch rather than cache a process-wide flag
+        if (smem > 48 * 1024)
+            CM_CUDA(cudaFuncSetAttribute(cm_boxblur3_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        cm_boxblur3_kernel<C><<<grid, 256, smem, b->stream>>>(
+            src, src_req_stride, dst, dst_req_stride, n, line_stride, (const BoxParams *)params, 3);
+    }
     cm::count_launch();
     CM_CUDA(cudaGetLastError());
     return CM_OK;
@@ -316,13 +465,16 @@ int cm_blur_set_image(cm_blur *b, const uint8_t *pixels, int height, int width) 
 static int upload_params(cm_blur *b, const float *radii, int n) {
     if (b->h == 0) return fail(CM_ERR_STATE, "cm_blur_set_image has not been called");
     std::vector<BoxParams> params((size_t)n);
+    int max_radius = 0;
     for (int i = 0; i < n; ++i) {
         // Pillow squares the radius (_gaussian_blur_radius), so GaussianBlur(-r) == GaussianBlur(r): a
         // cosine that rounds to 1.0000001 makes score_to_blur slightly negative in the reference too
         if (!(fabsf(radii[i]) <= 4096.0f))
             return fail(CM_ERR_INVALID, "radius %g of request %d outside [-4096, 4096]", (double)radii[i], i);
         params[(size_t)i] = box_params(radii[i]);
+        if (!params[(size_t)i].identity && params[(size_t)i].radius > max_radius) max_radius = params[(size_t)i].radius;
     }
+    b->max_box_radius = max_radius;
     // pageable source: the runtime stages it before returning, so `params` may go out of scope
     CM_CUDA(cudaMemcpyAsync(b->d_params, params.data(), sizeof(BoxParams) * n, cudaMemcpyHostToDevice, b->stream));
     return CM_OK;

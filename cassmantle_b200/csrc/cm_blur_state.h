@@ -17,6 +17,7 @@ struct cm_blur {
     uint8_t *d_b = nullptr;           // pong
     uint8_t *h_pin = nullptr;         // pinned staging for results
     void *d_params = nullptr;         // BoxParams[max_batch]
+    int max_box_radius = 0;           // largest box radius among the uploaded requests (chooses the blur kernel)
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;   // results of chunk i travel while chunk i+1 is blurred
     cudaEvent_t blurred[2] = {nullptr, nullptr};
