@@ -1070,6 +1070,29 @@ def run_own(args) -> None:
         eng.set_answers(ans)
         eng.synchronize()
 
+    # ---- the per-session image of a round: Gaussian blur + JPEG file (src/server.py:129-133, main.py:100-107) ----
+    image_leg = None
+    if rank == 0 and world == 1 and not args.no_other_shapes:
+        from cassmantle_b200.blur import ImageBlur
+        rng = np.random.default_rng(3)
+        yy, xx = np.mgrid[0:1024, 0:1024]
+        photo = np.stack([(xx + yy) % 256, (xx * 3) % 256, (yy * 7 + xx // 3) % 256], -1).astype(np.uint8)
+        photo = np.clip(photo.astype(int) + rng.integers(-9, 9, photo.shape), 0, 255).astype(np.uint8)
+        image_leg = {"workload": "1024x1024 RGB image, per-session GaussianBlur(score_to_blur(score)) + JPEG quality 75, "
+                                 "files in page-locked memory (byte-identical to Pillow: tests/test_gpu_jpeg.py)"}
+        for nb in (1, 8):
+            blur = ImageBlur(1024, 1024, 3, max_batch=nb)
+            blur.set_image(photo)
+            scores_img = rng.uniform(0.01, 1.0, nb)
+            for _ in range(5):
+                blur.mask_images_jpeg(scores_img)
+            tsi = []
+            for _ in range(20):
+                t1 = time.perf_counter(); files = blur.mask_images_jpeg(scores_img); tsi.append(time.perf_counter() - t1)
+            image_leg[f"batch_{nb}_us_per_image"] = float(np.median(tsi)) * 1e6 / nb
+            image_leg[f"batch_{nb}_kb_per_file"] = sum(len(f) for f in files) / nb / 1e3
+            blur.close()
+
     clocks = dict(timed_clocks, remeasured=bool(attempt))
 
     # ---- parity spot check of the timed path against the CPU sample ----------------------
@@ -1101,7 +1124,7 @@ def run_own(args) -> None:
             "sustained": sustained,
             "e2e": e2e, "gpu_launches": gpu_launches, "roofline": roofline,
             "cpu_baseline": cpu_baseline, "clocks": clocks, "latency": lat, "parity": parity,
-            "other_shapes": other, "python_boundary": py_lat, "most_similar": similar,
+            "other_shapes": other, "python_boundary": py_lat, "most_similar": similar, "image_blur_jpeg": image_leg,
         }
         print(json.dumps(line), flush=True)
     if gather is not None:
