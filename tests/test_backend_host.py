@@ -98,3 +98,38 @@ def test_pack_words_format():
 def test_lookup_oracle_first_occurrence_wins():
     rows = O.lookup_rows(["a", "B", "a", "b"], ["A", "b", "B", "c", ""])
     assert rows.tolist() == [0, 3, 3, -1, -1]
+
+
+def test_most_similar_many_is_most_similar_per_word():
+    """Backend.most_similar_many (one engine call for all words) against most_similar per word, with the oracle
+    standing in for both engine calls: key lookup through lower(), the query word dropped, topn kept, errors."""
+    from cassmantle_b200 import synth
+    import pytest
+    keys = synth.make_vocab(400, seed=0)
+    table = synth.table_rows(np.arange(400), seed=0)
+
+    class SimilarEngine:
+        batch_calls = 0
+
+        def most_similar(self, row, k):
+            d = O.most_similar_dists(table, int(row))
+            order = np.lexsort((np.arange(len(d)), -d))[:k]
+            return order.astype(np.int32), d[order].astype(np.float32)
+
+        def most_similar_batch(self, rows, k):
+            self.batch_calls += 1
+            return [self.most_similar(r, k) for r in rows]
+
+    eng = SimilarEngine()
+    be = Backend(eng, Vocabulary(keys), min_score=0.01)
+    words = [keys[3].upper(), keys[77], keys[399]]
+    many = be.most_similar_many(words, topn=7)
+    assert eng.batch_calls == 1 and len(many) == 3
+    for w, got in zip(words, many):
+        assert got == be.most_similar(w, topn=7)
+        assert len(got) == 7 and w.lower() not in [k for k, _ in got]
+        assert all(isinstance(s, float) for _, s in got)
+    assert be.most_similar_many([], topn=5) == []
+    with pytest.raises(Exception) as exc:
+        be.most_similar_many([keys[1], "no-such-word"], topn=5)
+    assert exc.value.args[0] == "Word not in dictionary. "
